@@ -1,0 +1,172 @@
+"""Pin the oracle (CPU only).
+
+The restatement in oracle/oracle.c must agree with
+  * the committed golden vectors (tests/golden/, produced by the reference's own gold code), and
+  * the reference gold compiled unmodified (oracle/_ref/libref_gold.so) whenever that file exists.
+"""
+import numpy as np
+import pytest
+
+import oracle
+
+HAVE_REF = oracle.ref is not None
+needs_ref = pytest.mark.skipif(not HAVE_REF, reason="oracle/_ref/libref_gold.so not built")
+
+
+def hx(a):
+    return "%016x" % oracle.fnv1a64(a)
+
+
+def test_fnv_known_answer():
+    # FNV-1a 64 test vectors (draft-eastlake-fnv): "" and "a"
+    assert oracle.fnv1a64(np.zeros(0, np.uint8)) == 0xcbf29ce484222325
+    assert oracle.fnv1a64(np.frombuffer(b"a", np.uint8)) == 0xaf63dc4c8601ec8c
+
+
+# ------------------------------------------------------------------------------- small fixtures
+def test_histogram_small_golden(golden_small):
+    g = golden_small
+    assert (oracle.histogram256(g["hist_in"]) == g["hist256_out"]).all()
+    assert (oracle.histogram64(g["hist_in"]) == g["hist64_out"]).all()
+    # the identity the fused multi-GPU path relies on: hist64[v] = sum of hist256[4v..4v+3]
+    assert (g["hist256_out"].reshape(64, 4).sum(1, dtype=np.uint32) == g["hist64_out"]).all()
+
+
+@pytest.mark.parametrize("L", [4, 32, 1024, 2048, 8192])
+def test_scan_small_golden(golden_small, L):
+    src = golden_small["scan_in"]
+    assert (oracle.scan_exclusive(src, src.size // L, L) == golden_small["scan_out_L%d" % L]).all()
+
+
+@pytest.mark.parametrize("name", ["d1", "d2", "d3"])
+@pytest.mark.parametrize("direction", [1, 0])
+def test_merge_sort_host_small_golden(golden_small, name, direction):
+    g = golden_small
+    keys = g["sort_%s_keys" % name]
+    vals = np.arange(keys.size, dtype=np.uint32)
+    mk, mv = oracle.merge_sort_host(keys, vals, direction)
+    assert (mk == g["sort_%s_dir%d_msh_keys" % (name, direction)]).all()
+    assert (mv == g["sort_%s_dir%d_msh_vals" % (name, direction)]).all()
+    sk, sv = oracle.stable_sort_kv(keys, vals, direction)
+    assert (sk == mk).all()
+    if name in ("d1", "d2"):
+        # keys unique inside every 1024-aligned tile => mergeSortHost coincides with the stable sort
+        assert (sv == mv).all()
+    else:
+        # duplicates inside tiles: the reference's CPU emulation is NOT stable
+        assert (sv != mv).any()
+    ok, stable = oracle.validate_sorted_values(sk, sv, keys)
+    assert ok == 1 and stable == 1
+    if name == "d3":  # validateSortedKeys needs keys < numValues (mergeSort_validate.cpp:50-70)
+        assert oracle.validate_sorted_keys(sk, keys, 64, direction) == 1
+
+
+def test_stable_sort_matches_numpy():
+    rng = np.random.default_rng(5)
+    for n in (0, 1, 2, 3, 1000, 4097):
+        k = rng.integers(0, 17, n, dtype=np.uint32)
+        v = np.arange(n, dtype=np.uint32)
+        sk, sv = oracle.stable_sort_kv(k, v, 1)
+        order = np.argsort(k, kind="stable")
+        assert (sk == k[order]).all() and (sv == v[order]).all()
+        sk, sv = oracle.stable_sort_kv(k, v, 0)
+        order = np.argsort(~k, kind="stable")  # descending, ties in source order
+        assert (sk == k[order]).all() and (sv == v[order]).all()
+
+
+# ------------------------------------------------------------------- the samples' default inputs
+def test_kat_histogram(kat):
+    d = oracle.sample_input("hist_bytes", kat["histogram256"]["bytes"], kat["histogram256"]["seed"])
+    h = oracle.histogram256(d)
+    assert (int(h[0]), int(h[255]), hx(h)) == (kat["histogram256"]["h0"], kat["histogram256"]["h255"],
+                                               kat["histogram256"]["fnv"])
+    # SURVEY.md 8c spot values
+    assert (int(h[0]), int(h[255])) == (262441, 262682)
+    h = oracle.histogram64(d)
+    assert (int(h[0]), int(h[63]), hx(h)) == (kat["histogram64"]["h0"], kat["histogram64"]["h63"],
+                                              kat["histogram64"]["fnv"])
+    assert (int(h[0]), int(h[63])) == (1048397, 1049943)
+
+
+def test_kat_scan(kat):
+    n = kat["scan"]["n"]
+    a = oracle.sample_input("scan_u32", n, kat["scan"]["seed"])
+    survey_last = {4: 1983869552, 1024: 3998548728, 2048: 2063854727, 262144: 972374877}
+    for case in kat["scan"]["cases"]:
+        L = case["L"]
+        s = oracle.scan_exclusive(a, n // L, L)
+        assert int(s[-1]) == case["last"] and hx(s) == case["fnv"]
+        if L in survey_last:
+            assert int(s[-1]) == survey_last[L]
+
+
+def test_kat_reduce(kat):
+    for case in kat["reduce"]["cases"]:
+        n = case["n"]
+        ri = oracle.sample_input("reduce_i32", n, 1)
+        assert oracle.reduce(ri) == case["i32"] == int(ri.astype(np.int64).sum())
+        rf = oracle.sample_input("reduce_f32", n, 1)
+        got = oracle.reduce(rf)
+        assert float(np.float32(got)).hex() == case["f32_hex"]
+        # Kahan fp32 is within 1 ulp-ish of the exact (fp64) sum
+        assert abs(got - float(rf.astype(np.float64).sum())) <= 2e-7 * abs(got)
+        rd = oracle.sample_input("reduce_f64", n, 1)
+        assert oracle.reduce(rd).hex() == case["f64_hex"]
+
+
+def test_reduce_int_wraps():
+    # reduceCPU<int> is a wrapping 32-bit sum (SURVEY.md 8c KAT-RED)
+    x = np.full(1 << 16, 0x7FFF, np.int32)
+    want = ((0x7FFF << 16) + 2**31) % 2**32 - 2**31
+    assert oracle.reduce(x) == want
+
+
+def test_kat_merge_sort(kat):
+    m = kat["mergeSort"]
+    k = oracle.sample_input("sort_keys", m["n"], m["seed"])
+    v = oracle.fill_values(m["n"])
+    sk, sv = oracle.stable_sort_kv(k, v, m["dir"])
+    assert hx(sk) == m["stable"]["fnv_keys"] and hx(sv) == m["stable"]["fnv_vals"]
+    mk, mv = oracle.merge_sort_host(k, v, m["dir"])
+    assert hx(mk) == m["mergeSortHost"]["fnv_keys"] and hx(mv) == m["mergeSortHost"]["fnv_vals"]
+    assert int((mv != sv).sum()) == m["mergeSortHost_vals_differing_from_stable"] == 21848
+    assert oracle.validate_sorted_keys(sk, k, 65536, 1) == 1
+    assert oracle.validate_sorted_values(sk, sv, k) == (1, 1)
+    assert oracle.validate_sorted_values(mk, mv, k) == (1, 0)  # the reference's own emulation: NOT stable
+
+
+# ---------------------------------------------------------- against the compiled reference gold
+@needs_ref
+def test_restatement_equals_reference_gold_random():
+    rng = np.random.default_rng(11)
+    for nbytes in (0, 4, 64, 4096, 1 << 20):
+        d = rng.integers(0, 256, nbytes, dtype=np.uint8)
+        assert (oracle.histogram256(d) == oracle.ref.histogram256(d)).all()
+        assert (oracle.histogram64(d) == oracle.ref.histogram64(d)).all()
+    for batch, L in ((1, 1), (3, 5), (7, 1024), (1, 1 << 20), (64, 4096)):
+        s = rng.integers(0, 2**32, batch * L, dtype=np.uint32)
+        assert (oracle.scan_exclusive(s, batch, L) == oracle.ref.scan_exclusive(s, batch, L)).all()
+    for n in (1, 2, 1000, 1024, 1025, 3 * 1024, 5000, 65536 + 17):
+        for direction in (1, 0):
+            k = rng.integers(0, 300, n, dtype=np.uint32)
+            v = np.arange(n, dtype=np.uint32)
+            a = oracle.merge_sort_host(k, v, direction)
+            b = oracle.ref.merge_sort_host(k, v, direction)
+            assert (a[0] == b[0]).all() and (a[1] == b[1]).all()
+            assert oracle.validate_sorted_keys(a[0], k, 300, direction) == \
+                oracle.ref.validate_sorted_keys(a[0], k, 300, direction) == 1
+            assert oracle.validate_sorted_values(a[0], a[1], k)[0] == oracle.ref.validate_sorted_values(a[0], a[1], k)
+
+
+def test_generator_is_counter_based():
+    # any window of the stream can be regenerated on its own (what lets 8 GPUs fill shards in place)
+    for kind, param in (("bytes", 0), ("u31", 0), ("i32_byte", 0), ("f32_byte", 0), ("key_unique", 0),
+                        ("key_tile_unique", 2048), ("key_mod", 65536), ("f64_byte", 0)):
+        whole = oracle.generate(kind, 0, 5000, 2009, param)
+        part = oracle.generate(kind, 1237, 2000, 2009, param)
+        assert (whole[1237:3237] == part).all()
+    k = oracle.generate("key_unique", 0, 1 << 16, 3)
+    assert np.unique(k).size == k.size
+    k = oracle.generate("key_tile_unique", 0, 8192, 0, 2048)
+    for t in range(8):
+        assert np.unique(k[t * 1024:(t + 1) * 1024]).size == 1024
