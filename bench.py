@@ -1,0 +1,408 @@
+#!/usr/bin/env python3
+"""bench.py -- throughput of the primitive hot path on B200, one JSON line on stdout (rank 0).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--skip-table]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Headline workload (BASELINE.json configs[1]): one step = reduce<int> + reduce<float> SUM over 2^28
+elements each, resident in HBM (2 GiB of algorithmic bytes per step, inputs 8x larger than L2).
+At N GPUs every rank reduces its own 2^28-element shards and the shard sums are combined with NCCL
+(weak scaling).  `value` = bytes all ranks reduced / max-over-ranks device time.
+`e2e` = the same step through the host-buffer C ABI (b200_reduce_*_host): pinned host inputs, H2D inside
+the timed region, result read back.  `primitives` carries the same measurement for every other primitive
+of the path (histogram64/256, scan, key-value sort) with its own roofline fraction.
+`--impl reference` times the samples' CPU gold path (reduceCPU, restated in oracle/) on the host cores.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "HBM GB/s (% of B200 peak) per primitive; sort Gkeys/s at 1/2/4/8 GPUs"
+N_ELEMS = 1 << 28
+WORKLOAD = "reduce<int> + reduce<float> SUM over 2^28 elements each per GPU (BASELINE configs[1])"
+HBM_NOMINAL = 8000.0
+HBM_FALLBACK = 6650.0  # /opt/skills/guides/B200_PROFILING.md, only when MEASURED_PEAKS.json is absent
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return HBM_FALLBACK, "fallback (B200_PROFILING.md)"
+
+
+def base_config(n_gpus):
+    return {"workload": WORKLOAD, "elements_per_gpu": N_ELEMS, "bytes_per_step_per_gpu": 2 * 4 * N_ELEMS,
+            "l2_policy": "inputs (1 GiB each) larger than L2 (126 MB); no flush needed",
+            "parallelism": "shard%d" % n_gpus, "seed": 1, "generator": "splitmix64 counter-based (oracle_generate twin)"}
+
+
+# ------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    """nvidia-smi poller (the recipe's clocks line) running while the GPU is under the bench load."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            self.proc = subprocess.Popen(["nvidia-smi", "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)],
+                                         stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if not self.proc:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        try:
+            for line in open(self.path):
+                f = [x.strip() for x in line.split(",")]
+                if len(f) < 9:
+                    continue
+                try:
+                    sm.append(float(f[1]))
+                    mx.append(float(f[2]))
+                except ValueError:
+                    continue
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"),
+                                   f[5:9]):
+                    if v == "Active":
+                        reasons.add(name)
+            os.remove(self.path)
+        except Exception:
+            pass
+        if sm:
+            out.update(sm_mhz=statistics.median(sm), sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+# ------------------------------------------------------------------------------------------ timing
+def time_steps(torch, fn, steps, warmup, barrier=None):
+    """W untimed steps, then exactly K steps between CUDA events on the current stream; -> seconds."""
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    if barrier:
+        barrier()
+        torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    if barrier:
+        barrier()
+    return e0.elapsed_time(e1) * 1e-3
+
+
+def max_over_ranks(torch, dist, seconds, world):
+    if world == 1:
+        return seconds
+    t = torch.tensor([seconds], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+# -------------------------------------------------------------------------------- reference arm (CPU)
+def cpu_reduce_parallel(oracle, np, pool, xi, xf, threads):
+    """Chunk-parallel harness around the gold reduceCPU: one contiguous chunk per thread, partials added up."""
+    bounds = np.linspace(0, xi.size, threads + 1).astype(np.int64)
+    jobs = [pool.submit(oracle.reduce, xi[bounds[i]:bounds[i + 1]]) for i in range(threads)]
+    jobs += [pool.submit(oracle.reduce, xf[bounds[i]:bounds[i + 1]]) for i in range(threads)]
+    res = [j.result() for j in jobs]
+    si = sum(res[:threads]) & 0xFFFFFFFF
+    sf = float(np.float64(sum(res[threads:])))
+    return si, sf
+
+
+def run_reference(args):
+    """The samples' CPU gold path for the headline workload (reduceCPU<int> + reduceCPU<float>), timed on
+    the host cores with every thread it can use.  Rank 0 only."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    import concurrent.futures
+
+    import numpy as np
+
+    import oracle
+    threads = len(os.sched_getaffinity(0))
+    sample = 1 << 26  # elements per dtype per step: bounded so K steps end within minutes
+    xi = oracle.generate("i32_byte", 0, sample, 1)
+    xf = oracle.generate("f32_byte", 0, sample, 1)
+    pool = concurrent.futures.ThreadPoolExecutor(max_workers=threads)
+    for _ in range(max(args.warmup, 1)):
+        cpu_reduce_parallel(oracle, np, pool, xi, xf, threads)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_reduce_parallel(oracle, np, pool, xi, xf, threads)
+    dt = time.perf_counter() - t0
+    gbs = args.steps * 2 * 4 * sample / dt / 1e9
+    line = {"impl": "reference", "metric": METRIC, "value": gbs, "unit": "GB/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "i32+f32",
+            "data": "synthetic", "config": base_config(args.gpus),
+            "cpu_baseline": {"value": gbs, "unit": "GB/s", "cores": threads, "kind": "port",
+                             "sample": "reduceCPU<int>+reduceCPU<float> (Kahan, reduction.cpp:167-180 restated in "
+                                       "oracle/oracle.c) over 2^26 elements each per step, one contiguous chunk per "
+                                       "thread, partials added"},
+            "e2e": {"value": gbs, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------- primitives table
+def primitives_table(torch, dist, prim, mg, rank, world, peak, barrier):
+    """GB/s (Gkeys/s for sort) of every primitive of the path, device-resident inputs, CUDA events."""
+    table = {}
+
+    def record(name, seconds_per_call, alg_bytes, extra=None):
+        t = max_over_ranks(torch, dist, seconds_per_call, world)
+        gbs = alg_bytes / t / 1e9
+        row = {"GB/s": round(gbs, 1), "us_per_call": round(t * 1e6, 2), "algorithmic_bytes": alg_bytes,
+               "frac_of_measured_peak": round(gbs / (peak * world), 4),
+               "frac_of_nominal_8TBs": round(gbs / (HBM_NOMINAL * world), 4), "n_gpus": world}
+        if extra:
+            row.update(extra)
+        table[name] = row
+
+    # --- histogram, 64 MiB (BASELINE configs[0]); 4 rotating inputs = 256 MiB > L2 so every call reads HBM
+    n64 = 64 << 20
+    bufs = [torch.empty(n64, dtype=torch.uint8, device="cuda") for _ in range(4)]
+    for i, b in enumerate(bufs):
+        prim.generate(b, "bytes", i * n64, n64, 2009)
+    h256 = torch.empty(256, dtype=torch.int32, device="cuda")
+    h64 = torch.empty(64, dtype=torch.int32, device="cuda")
+    it = [0]
+
+    def step256():
+        prim.histogram256(h256, bufs[it[0] & 3], n64)
+        it[0] += 1
+
+    def step64():
+        prim.histogram64(h64, bufs[it[0] & 3], n64)
+        it[0] += 1
+    record("histogram256_64MiB", time_steps(torch, step256, 40, 8) / 40, n64, {"l2": "4 rotating inputs (256 MiB)"})
+    record("histogram64_64MiB", time_steps(torch, step64, 40, 8) / 40, n64, {"l2": "4 rotating inputs (256 MiB)"})
+    del bufs
+    # --- histogram, 4 GiB per GPU, both histograms in one pass (BASELINE configs[3] shape: 32 GiB over 8)
+    big = 4 << 30
+    d = torch.empty(big, dtype=torch.uint8, device="cuda")
+    prim.generate(d, "bytes", rank * big, big, 2009)
+
+    def step_fused():
+        mg.histogram_sharded(d, big)
+    record("histogram64+256_fused_4GiB_per_gpu", time_steps(torch, step_fused, 5, 2, barrier) / 5, big * world,
+           {"scaling": "weak", "collective": "all_reduce(320 x u32)" if world > 1 else None,
+            "note": "1 B per input byte for BOTH histograms (one pass)"})
+    h256b = torch.empty(256, dtype=torch.int32, device="cuda")
+
+    def step_256_big():
+        prim.histogram256(h256b, d, big)
+    record("histogram256_4GiB", time_steps(torch, step_256_big, 5, 2) / 5, big * world, {"scaling": "weak"})
+    del d
+    # --- scan, 2^28 u32 in total (BASELINE configs[2]: strong scaling, carry via all_gather of shard totals)
+    n = N_ELEMS // world
+    src = torch.empty(n, dtype=torch.int32, device="cuda")
+    dst = torch.empty(n, dtype=torch.int32, device="cuda")
+    prim.generate(src, "u31", rank * n, n, 2009)
+
+    def step_scan():
+        mg.scan_sharded(dst, src, n)
+    record("scanExclusiveLarge_2^28", time_steps(torch, step_scan, 20, 4, barrier) / 20, 8 * N_ELEMS,
+           {"scaling": "strong", "collective": "all_gather(G x u32)" if world > 1 else None})
+    if world == 1:
+        def step_scan_short():
+            prim.scanExclusiveShort(dst, src, n // 1024, 1024)
+        record("scanExclusiveShort_L1024_2^28", time_steps(torch, step_scan_short, 20, 4) / 20, 8 * N_ELEMS)
+    del src, dst
+    # --- key-value sort, 2^28 pairs in total (BASELINE configs[4]), dataset D1 (all keys distinct)
+    sk = torch.empty(n, dtype=torch.int32, device="cuda")
+    sv = torch.arange(rank * n, rank * n + n, dtype=torch.int64, device="cuda").to(torch.int32)
+    prim.generate(sk, "key_unique", rank * n, n, 2009)
+    if world == 1:
+        dk, dv, bk, bv = (torch.empty(n, dtype=torch.int32, device="cuda") for _ in range(4))
+
+        def step_sort():
+            prim.mergeSort(dk, dv, bk, bv, sk, sv, n, 1)
+    else:
+        def step_sort():
+            mg.sort_sharded(sk, sv, n, 1)
+    ts = time_steps(torch, step_sort, 5, 2, barrier) / 5
+    t = max_over_ranks(torch, dist, ts, world)
+    table["mergeSort_kv_2^28"] = {
+        "Gkeys/s": round(N_ELEMS / t / 1e9, 3), "ms_per_call": round(t * 1e3, 3), "n_gpus": world,
+        "traffic_model_bytes_per_pair": 68, "GB/s_at_68B_per_pair": round(68 * N_ELEMS / t / 1e9, 1),
+        "frac_of_measured_peak": round(68 * N_ELEMS / t / 1e9 / (peak * world), 4),
+        "frac_of_nominal_8TBs": round(68 * N_ELEMS / t / 1e9 / (HBM_NOMINAL * world), 4),
+        "scaling": "strong", "dataset": "D1 unique keys, val=i, ascending",
+        "collective": "sample sort: all_gather + all_to_all" if world > 1 else None}
+    return table
+
+
+# --------------------------------------------------------------------------------------------- ours
+def run_ours(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    import cuda_samples_b200 as prim
+    from cuda_samples_b200 import multi_gpu as mg
+
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    barrier = (lambda: dist.barrier()) if world > 1 else None
+    peak, peak_src = measured_peak()
+
+    # ---- inputs, resident in HBM (each rank generates its own slice of the global stream)
+    xi = torch.empty(N_ELEMS, dtype=torch.int32, device="cuda")
+    xf = torch.empty(N_ELEMS, dtype=torch.float32, device="cuda")
+    prim.generate(xi, "i32_byte", rank * N_ELEMS, N_ELEMS, 1)
+    prim.generate(xf, "f32_byte", rank * N_ELEMS, N_ELEMS, 1)
+    res = {}
+
+    def step():
+        res["i"] = mg.reduce_sharded(xi, N_ELEMS)
+        res["f"] = mg.reduce_sharded(xf, N_ELEMS)
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    launches0 = prim.launch_count()
+    seconds = time_steps(torch, step, args.steps, args.warmup, barrier)
+    launches = prim.launch_count() - launches0 - 2 * args.warmup
+    seconds = max_over_ranks(torch, dist, seconds, world)
+    # keep the same load running ~1.5 s so the 100 ms clock poller sees it (untimed)
+    t_end = time.perf_counter() + 1.5
+    while time.perf_counter() < t_end:
+        for _ in range(50):
+            step()
+        torch.cuda.synchronize()
+    clocks = sampler.stop() if rank == 0 else None
+    gpu_i, gpu_f = int(res["i"].item()), float(res["f"].item())
+
+    bytes_per_step = 2 * 4 * N_ELEMS * world
+    value = bytes_per_step * args.steps / seconds / 1e9
+    per_launch_s = seconds / (2 * args.steps)  # the timed region holds only reduce_kernel launches (+NCCL at N>1)
+    achieved = 4 * N_ELEMS / per_launch_s / 1e9
+
+    # ---- e2e: host buffers in, result out, copies inside the timed region (C ABI: b200_reduce_*_host)
+    hi = torch.empty(N_ELEMS, dtype=torch.int32, pin_memory=True)
+    hf = torch.empty(N_ELEMS, dtype=torch.float32, pin_memory=True)
+    hi.copy_(xi)
+    hf.copy_(xf)
+    torch.cuda.synchronize()
+    e2e_steps = max(1, min(args.steps, 10))
+    for _ in range(2):
+        prim.reduce_host(hi), prim.reduce_host(hf)
+    if barrier:
+        barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e_i, e_f = prim.reduce_host(hi), prim.reduce_host(hf)
+    e2e_s = time.perf_counter() - t0
+    e2e_s = max_over_ranks(torch, dist, e2e_s, world)
+    e2e_value = bytes_per_step * e2e_steps / e2e_s / 1e9
+
+    table = None
+    if not args.skip_table:
+        del xi, xf
+        torch.cuda.empty_cache()
+        try:
+            table = primitives_table(torch, dist, prim, mg, rank, world, peak, barrier)
+        except Exception as e:  # the headline must still be printed
+            table = {"error": repr(e)}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- CPU baseline on rank 0 (N=1 only): the gold path, single thread as shipped, whole workload once
+    cpu = None
+    parity = None
+    if world == 1:
+        import oracle
+        a, b = hi.numpy(), hf.numpy()
+        t0 = time.perf_counter()
+        cpu_i = oracle.reduce(a)
+        cpu_f = oracle.reduce(b)
+        dt = time.perf_counter() - t0
+        cpu = {"value": 2 * 4 * N_ELEMS / dt / 1e9, "unit": "GB/s", "cores": 1, "kind": "port",
+               "sample": "reduceCPU<int> + reduceCPU<float> (Kahan) once over the full 2^28-element inputs, "
+                         "single thread as shipped (reduction.cpp:167-180 restated in oracle/oracle.c)"}
+        parity = {"int_bit_exact": cpu_i == gpu_i == e_i,
+                  "float_rel_err": abs(gpu_f - cpu_f) / abs(cpu_f), "float_rel_err_e2e": abs(e_f - cpu_f) / abs(cpu_f),
+                  "float_tolerance": 1e-5}
+
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            traffic = json.load(f).get("reduce_kernel")
+    except Exception:
+        pass
+    cfg = base_config(world)
+    cfg["clock_probe"] = "same step looped ~1.5 s after the timed region for the 100 ms nvidia-smi poller"
+    line = {"metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": seconds / args.steps * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "i32+f32", "data": "synthetic", "config": cfg,
+            "roofline": {"bound": "hbm", "kernel": "reduce_kernel<int|float>", "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
+                         "frac_of_nominal_8TBs": achieved / HBM_NOMINAL, "traffic": traffic,
+                         "algorithmic_bytes_per_launch": 4 * N_ELEMS},
+            "cpu_baseline": cpu, "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": 2 * 4 * N_ELEMS,
+                    "d2h_bytes_per_step": 8, "steps": e2e_steps,
+                    "api": "b200_reduce_i32_host + b200_reduce_f32_host (pinned host input, chunked H2D overlap)"},
+            "gpu_launches": int(launches), "parity": parity, "primitives": table}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--skip-table", action="store_true", help="headline only (no per-primitive table)")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,214 @@
+"""Host-side mirror of the samples' entry points (same names, same argument meaning) over the C ABI.
+
+Device buffers are anything with a `data_ptr()` (torch CUDA tensors) or a raw integer device pointer;
+work is enqueued on torch's current CUDA stream.  PyTorch is only plumbing here (device memory,
+streams); the arithmetic happens in libb200prim.so.
+
+Reference interfaces mirrored (paths relative to /root/reference/Samples):
+  histogram64 / histogram256 / init* / close*   2_Concepts_and_Techniques/histogram/histogram_common.h:75-82
+  reduce(size, threads, blocks, whichKernel, d_idata, d_odata)
+                                                2_Concepts_and_Techniques/reduction/reduction.h:32
+  scanExclusiveShort / scanExclusiveLarge / initScan / closeScan
+                                                2_Concepts_and_Techniques/scan/scan_common.h:41-55
+  mergeSort / initMergeSort / closeMergeSort    0_Introduction/mergeSort/mergeSort_common.h:49-54
+"""
+import ctypes
+
+import numpy as np
+
+from ._lib import B200Error, check, const_u32, lib
+
+HISTOGRAM64_BIN_COUNT = 64
+HISTOGRAM256_BIN_COUNT = 256
+MAX_BATCH_ELEMENTS = const_u32("MAX_BATCH_ELEMENTS")
+MIN_SHORT_ARRAY_SIZE = const_u32("MIN_SHORT_ARRAY_SIZE")
+MAX_SHORT_ARRAY_SIZE = const_u32("MAX_SHORT_ARRAY_SIZE")
+MIN_LARGE_ARRAY_SIZE = const_u32("MIN_LARGE_ARRAY_SIZE")
+MAX_LARGE_ARRAY_SIZE = const_u32("MAX_LARGE_ARRAY_SIZE")
+
+GEN_KINDS = {"bytes": 0, "u31": 1, "i32_byte": 2, "f32_byte": 3, "key_unique": 4, "key_tile_unique": 5,
+             "key_mod": 6, "f64_byte": 7}
+
+
+def _dptr(x):
+    if x is None:
+        return None
+    if isinstance(x, int):
+        return ctypes.c_void_p(x)
+    if hasattr(x, "data_ptr"):
+        if hasattr(x, "is_cuda") and not x.is_cuda:
+            raise B200Error("expected a CUDA tensor, got a host tensor")
+        if hasattr(x, "is_contiguous") and not x.is_contiguous():
+            raise B200Error("expected a contiguous tensor")
+        return ctypes.c_void_p(x.data_ptr())
+    raise TypeError("device buffer must be a CUDA tensor or an integer device pointer, got %r" % type(x))
+
+
+def _hptr(x):
+    if isinstance(x, np.ndarray):
+        if not x.flags["C_CONTIGUOUS"]:
+            raise B200Error("expected a C-contiguous array")
+        return ctypes.c_void_p(x.ctypes.data)
+    if hasattr(x, "data_ptr"):
+        if getattr(x, "is_cuda", False):
+            raise B200Error("expected a host tensor, got a CUDA tensor")
+        return ctypes.c_void_p(x.data_ptr())
+    if isinstance(x, int):
+        return ctypes.c_void_p(x)
+    raise TypeError(type(x))
+
+
+def _stream(stream=None):
+    if stream is None:
+        import torch
+        return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    if isinstance(stream, int):
+        return ctypes.c_void_p(stream)
+    return ctypes.c_void_p(stream.cuda_stream)
+
+
+def launch_count():
+    return int(lib.b200_launch_count())
+
+
+def device_info():
+    v = [ctypes.c_int(0) for _ in range(4)]
+    check(lib.b200_device_info(*[ctypes.byref(x) for x in v]), "b200_device_info")
+    return {"num_sms": v[0].value, "smem_optin": v[1].value, "cc": (v[2].value, v[3].value)}
+
+
+# ------------------------------------------------------------------------------------ histogram
+def initHistogram64():
+    lib.initHistogram64()
+
+
+def initHistogram256():
+    lib.initHistogram256()
+
+
+def closeHistogram64():
+    lib.closeHistogram64()
+
+
+def closeHistogram256():
+    lib.closeHistogram256()
+
+
+def histogram256(d_Histogram, d_Data, byteCount, stream=None):
+    """d_Histogram[256] (u32) <- byte counts of d_Data[0:byteCount]; overwritten, wraps mod 2^32."""
+    check(lib.b200_histogram256_async(_dptr(d_Histogram), _dptr(d_Data), byteCount, _stream(stream)), "histogram256")
+
+
+def histogram64(d_Histogram, d_Data, byteCount, stream=None):
+    """d_Histogram[64] (u32) <- counts of (byte >> 2)."""
+    check(lib.b200_histogram64_async(_dptr(d_Histogram), _dptr(d_Data), byteCount, _stream(stream)), "histogram64")
+
+
+def histogram_fused(d_Histogram256, d_Histogram64, d_Data, byteCount, stream=None):
+    """Both histograms from one pass over the data."""
+    check(lib.b200_histogram_fused_async(_dptr(d_Histogram256), _dptr(d_Histogram64), _dptr(d_Data), byteCount,
+                                         _stream(stream)), "histogram_fused")
+
+
+# ------------------------------------------------------------------------------------ reduction
+_REDUCE = {"torch.int32": "i32", "torch.float32": "f32", "torch.float64": "f64",
+           "int32": "i32", "float32": "f32", "float64": "f64"}
+
+
+def reduce(size, threads, blocks, whichKernel, d_idata, d_odata, stream=None):
+    """reduce<T>: afterwards sum(d_odata[0:blocks]) == sum(d_idata[0:size]); here d_odata[0] holds the
+    total and d_odata[1:blocks] zeros.  `threads` / `whichKernel` are accepted and ignored."""
+    kind = _REDUCE.get(str(d_idata.dtype))
+    if kind is None:
+        raise TypeError("reduce: unsupported dtype %s" % d_idata.dtype)
+    fn = getattr(lib, "b200_reduce_%s_async" % kind)
+    check(fn(_dptr(d_idata), size, _dptr(d_odata), max(int(blocks), 1), _stream(stream)), "reduce<%s>" % kind)
+
+
+# ----------------------------------------------------------------------------------------- scan
+def initScan():
+    lib.initScan()
+
+
+def closeScan():
+    lib.closeScan()
+
+
+def scanExclusiveShort(d_Dst, d_Src, batchSize, arrayLength, stream=None):
+    check(lib.b200_scan_exclusive_async(_dptr(d_Dst), _dptr(d_Src), batchSize, arrayLength, None, _stream(stream)),
+          "scanExclusiveShort")
+    return 512
+
+
+def scanExclusiveLarge(d_Dst, d_Src, batchSize, arrayLength, stream=None, d_carry=None):
+    """d_carry (optional, device u32): seed of element 0 -- the shard carry of the multi-GPU scan."""
+    check(lib.b200_scan_exclusive_async(_dptr(d_Dst), _dptr(d_Src), batchSize, arrayLength, _dptr(d_carry),
+                                        _stream(stream)), "scanExclusiveLarge")
+    return 512
+
+
+def scan_total(d_total, d_Src, n, stream=None):
+    check(lib.b200_scan_total_async(_dptr(d_total), _dptr(d_Src), n, _stream(stream)), "scan_total")
+
+
+# ------------------------------------------------------------------------------------ mergeSort
+def initMergeSort():
+    lib.initMergeSort()
+
+
+def closeMergeSort():
+    lib.closeMergeSort()
+
+
+def mergeSort(dstKey, dstVal, bufKey, bufVal, srcKey, srcVal, N, sortDir, stream=None):
+    """Stable key-value sort; result in dst*, buf* scratch, src* untouched; sortDir 1 asc / 0 desc."""
+    check(lib.b200_sort_kv_async(_dptr(dstKey), _dptr(dstVal), _dptr(bufKey), _dptr(bufVal), _dptr(srcKey),
+                                 _dptr(srcVal), N, sortDir, _stream(stream)), "mergeSort")
+
+
+def partition_kv(dstKey, dstVal, srcKey, srcVal, N, d_splitters, numBuckets, sortDir, d_bucketCounts, stream=None):
+    check(lib.b200_partition_kv_async(_dptr(dstKey), _dptr(dstVal), _dptr(srcKey), _dptr(srcVal), N,
+                                      _dptr(d_splitters), numBuckets, sortDir, _dptr(d_bucketCounts),
+                                      _stream(stream)), "partition_kv")
+
+
+# ------------------------------------------------------------------------------------- generator
+def generate(d_out, kind, first, n, seed, param=0, stream=None):
+    check(lib.b200_generate_async(_dptr(d_out), first, n, seed, GEN_KINDS[kind], param, _stream(stream)), "generate")
+
+
+# ---------------------------------------------------------------- host-buffer (end-to-end) variants
+def histogram256_host(h_data):
+    h = np.empty(256, np.uint32)
+    n = h_data.nbytes if isinstance(h_data, np.ndarray) else h_data.numel() * h_data.element_size()
+    check(lib.b200_histogram256_host(_hptr(h), _hptr(h_data), n), "histogram256_host")
+    return h
+
+
+def histogram64_host(h_data):
+    h = np.empty(64, np.uint32)
+    n = h_data.nbytes if isinstance(h_data, np.ndarray) else h_data.numel() * h_data.element_size()
+    check(lib.b200_histogram64_host(_hptr(h), _hptr(h_data), n), "histogram64_host")
+    return h
+
+
+def reduce_host(h_in):
+    name = str(h_in.dtype)
+    kind = _REDUCE.get(name)
+    if kind is None:
+        raise TypeError("reduce_host: unsupported dtype %s" % name)
+    n = h_in.size if isinstance(h_in, np.ndarray) else h_in.numel()
+    out = np.zeros(1, {"i32": np.int32, "f32": np.float32, "f64": np.float64}[kind])
+    check(getattr(lib, "b200_reduce_%s_host" % kind)(_hptr(h_in), n, _hptr(out)), "reduce_host")
+    return out[0].item()
+
+
+def scan_exclusive_host(h_dst, h_src, batchSize, arrayLength):
+    check(lib.b200_scan_exclusive_host(_hptr(h_dst), _hptr(h_src), batchSize, arrayLength), "scan_exclusive_host")
+    return h_dst
+
+
+def sort_kv_host(h_dstKey, h_dstVal, h_srcKey, h_srcVal, N, sortDir):
+    check(lib.b200_sort_kv_host(_hptr(h_dstKey), _hptr(h_dstVal), _hptr(h_srcKey), _hptr(h_srcVal), N, sortDir),
+          "sort_kv_host")
+    return h_dstKey, h_dstVal

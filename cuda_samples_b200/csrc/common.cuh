@@ -1,0 +1,195 @@
+// common.cuh -- shared device/host helpers for the sm_100a primitive library.
+//
+// Error convention (two layers, see include/b200prim.h):
+//   * the extended C ABI (b200_*) returns an int status: 0 or a cudaError_t value;
+//   * the drop-in entry points keep the samples' convention: print to stderr and
+//     exit(EXIT_FAILURE) (reference: Common/helper_cuda.h:584-616).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+
+#define B200_TRY(expr)                                                                                       \
+    do {                                                                                                     \
+        cudaError_t _e = (expr);                                                                             \
+        if (_e != cudaSuccess)                                                                               \
+            return (int)_e;                                                                                  \
+    } while (0)
+
+#define B200_OR_DIE(expr, what)                                                                              \
+    do {                                                                                                     \
+        int _s = (int)(expr);                                                                                \
+        if (_s != 0) {                                                                                       \
+            fprintf(stderr, "%s(%d): %s failed: CUDA error %d (%s)\n", __FILE__, __LINE__, what, _s,         \
+                    cudaGetErrorName((cudaError_t)_s));                                                      \
+            exit(EXIT_FAILURE);                                                                              \
+        }                                                                                                    \
+    } while (0)
+
+namespace b200 {
+
+constexpr int kWarp = 32;
+
+// ------------------------------------------------------------------------------------------------
+// Per-device scratch.  The reference keeps file-static scratch allocated by init*() (e.g.
+// histogram256.cu:133, scan.cu:182, mergeSort.cu:452); here every primitive asks the current
+// device's context for grow-only scratch, so a missing init*() is harmless and sizes are not capped.
+// Not thread-safe across host threads sharing a device -- same contract as the reference.
+// ------------------------------------------------------------------------------------------------
+struct Scratch {
+    void  *ptr   = nullptr;
+    size_t bytes = 0;
+};
+
+struct DeviceCtx {
+    int     device   = -1;
+    int     num_sms  = 0;
+    int     smem_max = 0; // opt-in dynamic shared memory per block
+    Scratch reduce;       // partials + ticket
+    Scratch hist;         // accumulators + ticket
+    Scratch scan;         // state + tile descriptors
+    Scratch sort;         // digit histograms + descriptors
+    Scratch stage[2];     // device staging chunks of the host-buffer entry points
+    cudaStream_t copy_stream[2] = {nullptr, nullptr}; // H2D / D2H engines of the host-buffer entry points
+    cudaStream_t compute_stream = nullptr;
+    cudaEvent_t  ev[6]          = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+};
+
+// Returns the context of the current device (created on first use).  nullptr + *status on error.
+DeviceCtx *ctx(int *status);
+// Grow-only allocation; newly allocated memory is zero-filled (stream-ordered on `stream`).
+int ensure(Scratch &s, size_t bytes, cudaStream_t stream, bool *fresh = nullptr);
+void release(Scratch &s);
+
+// ------------------------------------------------------------------------------------------------
+// PTX helpers
+// ------------------------------------------------------------------------------------------------
+// 128-bit streaming load: read-only path, do not allocate in L1 (each byte is touched once).
+__device__ __forceinline__ uint4 ld_stream_u4(const void *p)
+{
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p));
+    return r;
+}
+// same without .nc: for kernels that may run in place (the loaded line is later written by this CTA)
+__device__ __forceinline__ uint4 ld_once_u4(const void *p)
+{
+    uint4 r;
+    asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p)
+                 : "memory");
+    return r;
+}
+__device__ __forceinline__ void st_stream_u4(void *p, uint4 v)
+{
+    asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z),
+                 "r"(v.w)
+                 : "memory");
+}
+__device__ __forceinline__ unsigned lane_id()
+{
+    unsigned l;
+    asm("mov.u32 %0, %%laneid;" : "=r"(l));
+    return l;
+}
+__device__ __forceinline__ unsigned lanemask_lt()
+{
+    unsigned m;
+    asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+    return m;
+}
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+// relaxed / acquire / release accesses at gpu scope for the inter-CTA descriptors
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long *p)
+{
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed_u64(unsigned long long *p, unsigned long long v)
+{
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned ld_relaxed_u32(const unsigned *p)
+{
+    unsigned v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned *p)
+{
+    unsigned v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed_u32(unsigned *p, unsigned v)
+{
+    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void st_release_u32(unsigned *p, unsigned v)
+{
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// ---- mbarrier + 1-D bulk async copy (TMA engine; SASS: UBLKCP) -------------------------------------
+__device__ __forceinline__ void mbar_init(uint64_t *bar, unsigned count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void fence_mbar_init()
+{
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void fence_proxy_async_smem()
+{
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, unsigned bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, unsigned parity)
+{
+    asm volatile("{\n"
+                 ".reg .pred p;\n"
+                 "WAIT_%=:\n"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+                 "@p bra DONE_%=;\n"
+                 "bra WAIT_%=;\n"
+                 "DONE_%=:\n"
+                 "}" ::"r"(smem_u32(bar)),
+                 "r"(parity)
+                 : "memory");
+}
+// global -> shared, completion signalled on an mbarrier (bytes: multiple of 16, both 16-B aligned)
+__device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gsrc, unsigned bytes, uint64_t *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(smem_dst)),
+                 "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+// shared -> global, tracked by the bulk async-group
+__device__ __forceinline__ void bulk_s2g(void *gdst, const void *smem_src, unsigned bytes)
+{
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(smem_src)),
+                 "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void bulk_wait_read()
+{
+    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+template <int N> __device__ __forceinline__ void bulk_wait_all()
+{
+    asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
+}
+
+} // namespace b200

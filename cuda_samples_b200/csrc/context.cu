@@ -1,0 +1,140 @@
+// context.cu -- per-device scratch, launch accounting and the small utility exports of b200prim.h.
+#include "common.cuh"
+#include "internal.h"
+
+#include <atomic>
+#include <mutex>
+
+namespace b200 {
+
+static constexpr int kMaxDevices = 64;
+static DeviceCtx      g_ctx[kMaxDevices];
+static std::mutex     g_mutex;
+std::atomic<unsigned long long> g_launches{0};
+
+DeviceCtx *ctx(int *status)
+{
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+        if (status)
+            *status = (int)(e != cudaSuccess ? e : cudaErrorInvalidDevice);
+        return nullptr;
+    }
+    DeviceCtx &c = g_ctx[dev];
+    if (c.device < 0) {
+        std::lock_guard<std::mutex> lock(g_mutex);
+        if (c.device < 0) {
+            int major = 0;
+            e = cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
+            if (e == cudaSuccess)
+                e = cudaDeviceGetAttribute(&c.num_sms, cudaDevAttrMultiProcessorCount, dev);
+            if (e == cudaSuccess)
+                e = cudaDeviceGetAttribute(&c.smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+            if (e == cudaSuccess && major != 10)
+                e = cudaErrorNoKernelImageForDevice; // sm_100a only: fail loudly, there is no fallback
+            if (e != cudaSuccess) {
+                if (status)
+                    *status = (int)e;
+                return nullptr;
+            }
+            c.device = dev;
+        }
+    }
+    if (status)
+        *status = 0;
+    return &c;
+}
+
+int ensure(Scratch &s, size_t bytes, cudaStream_t stream, bool *fresh)
+{
+    if (fresh)
+        *fresh = false;
+    if (s.bytes >= bytes)
+        return 0;
+    // grow-only and rare (sizes settle after the first call): cudaFree synchronises the device, so
+    // work already enqueued on the old block has finished before it goes away.
+    if (s.ptr)
+        B200_TRY(cudaFree(s.ptr));
+    s.ptr   = nullptr;
+    s.bytes = 0;
+    size_t want = bytes < 4096 ? 4096 : bytes;
+    B200_TRY(cudaMalloc(&s.ptr, want));
+    B200_TRY(cudaMemsetAsync(s.ptr, 0, want, stream));
+    s.bytes = want;
+    if (fresh)
+        *fresh = true;
+    return 0;
+}
+
+void release(Scratch &s)
+{
+    if (s.ptr)
+        cudaFree(s.ptr);
+    s.ptr   = nullptr;
+    s.bytes = 0;
+}
+
+} // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_version(void) { return 100; }
+
+extern "C" const char *b200_error_string(int status)
+{
+    return status == 0 ? "success" : cudaGetErrorString((cudaError_t)status);
+}
+
+extern "C" int b200_device_info(int *num_sms, int *smem_optin, int *cc_major, int *cc_minor)
+{
+    int dev = 0, v = 0;
+    B200_TRY(cudaGetDevice(&dev));
+    if (num_sms) {
+        B200_TRY(cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev));
+        *num_sms = v;
+    }
+    if (smem_optin) {
+        B200_TRY(cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+        *smem_optin = v;
+    }
+    if (cc_major) {
+        B200_TRY(cudaDeviceGetAttribute(&v, cudaDevAttrComputeCapabilityMajor, dev));
+        *cc_major = v;
+    }
+    if (cc_minor) {
+        B200_TRY(cudaDeviceGetAttribute(&v, cudaDevAttrComputeCapabilityMinor, dev));
+        *cc_minor = v;
+    }
+    return 0;
+}
+
+extern "C" unsigned long long b200_launch_count(void) { return g_launches.load(); }
+
+extern "C" int b200_release_scratch(void)
+{
+    int        st = 0;
+    DeviceCtx *c  = ctx(&st);
+    if (!c)
+        return st;
+    B200_TRY(cudaDeviceSynchronize());
+    release(c->reduce);
+    release(c->hist);
+    release(c->scan);
+    release(c->sort);
+    release(c->stage[0]);
+    release(c->stage[1]);
+    return 0;
+}
+
+extern "C" int b200_host_alloc(void **h_ptr, size_t bytes)
+{
+    B200_TRY(cudaHostAlloc(h_ptr, bytes ? bytes : 1, cudaHostAllocDefault));
+    return 0;
+}
+
+extern "C" int b200_host_free(void *h_ptr)
+{
+    B200_TRY(cudaFreeHost(h_ptr));
+    return 0;
+}

@@ -1,0 +1,233 @@
+// histogram.cu -- byte histograms (256 bins, 64 bins, or both in one pass) for sm_100a.
+//
+// Replaces histogram256Kernel + mergeHistogram256Kernel (Samples/2_Concepts_and_Techniques/
+// histogram/histogram256.cu:54-126) and histogram64Kernel + mergeHistogram64Kernel
+// (histogram64.cu:67-158) with ONE launch and no partial-histogram buffer:
+//   * one persistent CTA of 1024 threads per SM, grid-stride 16-byte streaming loads, kUnroll in
+//     flight per thread;
+//   * counting: a shared-memory table laid out [bin][lane] (u32).  Lane l of every warp only ever
+//     touches column l, so bank == lane and every shared atomic of a warp is bank-conflict-free
+//     whatever the data is (uniform random, all-equal, ...) -- the reference's warp-private
+//     256-word tables serialise on same-bank bins (histogram256.cu:44-52);
+//   * merge: each warp folds 8 rows with redux.sync; non-leader CTAs of a thread-block cluster add
+//     their bins into the leader's shared memory through DSMEM (red.shared::cluster), the leader
+//     issues one red.global per bin into a zeroed accumulator; the last leader (atomic ticket)
+//     copies the accumulator to d_Histogram (overwrite semantics of the sample) and re-zeroes it.
+//   * histogram64 bin = byte >> 2 (the TOP six bits, histogram_gold.cpp:41-44); the fused mode
+//     derives it exactly from the 256-bin totals (hist64[v] = sum hist256[4v..4v+3]).
+// Roofline: HBM-bound by bytes (1 B per input byte) but paced by shared-atomic throughput
+// (one ATOMS lane-op per input byte); see DESIGN.md.
+#include <cooperative_groups.h>
+
+#include "common.cuh"
+#include "internal.h"
+
+namespace cg = cooperative_groups;
+
+namespace b200 {
+
+constexpr int kHistThreads = 1024;
+constexpr int kHistUnroll  = 4;
+
+enum HistMode { kHist256 = 0, kHist64 = 1, kHistFused = 2 };
+
+// scratch layout (u32 words): [0] ticket, [4..260) acc256, [260..324) acc64
+constexpr int kHistAcc256 = 4;
+constexpr int kHistAcc64  = 260;
+constexpr int kHistWords  = 324;
+
+template <int BINS, int SH> __device__ __forceinline__ void count_word(unsigned *table, unsigned lane4, unsigned w)
+{
+    // byte k of w -> bin = (byte >> SH); table byte offset = bin * 128 + lane * 4
+    constexpr unsigned kMask = (unsigned)(BINS - 1) << 7;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int s   = k * 8 + SH - 7;
+        unsigned  off = (s >= 0) ? (w >> (s >= 0 ? s : 0)) : (w << (s < 0 ? -s : 0));
+        off           = (off & kMask) | lane4;
+        atomicAdd(reinterpret_cast<unsigned *>(reinterpret_cast<char *>(table) + off), 1u);
+    }
+}
+
+template <int BINS, int SH> __device__ __forceinline__ void count_vec(unsigned *table, unsigned lane4, uint4 v)
+{
+    count_word<BINS, SH>(table, lane4, v.x);
+    count_word<BINS, SH>(table, lane4, v.y);
+    count_word<BINS, SH>(table, lane4, v.z);
+    count_word<BINS, SH>(table, lane4, v.w);
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(kHistThreads, 1)
+    histogram_kernel(const unsigned char *__restrict__ data, size_t n, unsigned *__restrict__ out256,
+                     unsigned *__restrict__ out64, unsigned *__restrict__ scratch)
+{
+    constexpr int BINS = (MODE == kHist64) ? 64 : 256;
+    constexpr int SH   = (MODE == kHist64) ? 2 : 0;
+    __shared__ unsigned table[BINS * 32];
+    __shared__ unsigned merged[BINS]; // the cluster leader's copy collects the whole cluster
+    __shared__ bool     s_last;
+
+    cg::cluster_group cluster = cg::this_cluster();
+    const unsigned    crank   = cluster.block_rank();
+    const unsigned    csize   = cluster.num_blocks();
+    const unsigned    lane    = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned    lane4   = lane * 4;
+
+    for (int i = threadIdx.x; i < BINS * 32; i += kHistThreads)
+        table[i] = 0;
+    if (threadIdx.x < BINS)
+        merged[threadIdx.x] = 0;
+    __syncthreads();
+
+    // ---- count ----------------------------------------------------------------------------------
+    const uintptr_t addr = (uintptr_t)data;
+    size_t          head = (16 - (addr & 15)) & 15;
+    if (head > n)
+        head = n;
+    const size_t nvec   = (n - head) / 16;
+    const size_t tail   = head + nvec * 16;
+    const uint4 *vin    = reinterpret_cast<const uint4 *>(data + head);
+    const size_t stride = (size_t)gridDim.x * kHistThreads;
+    size_t       v      = (size_t)blockIdx.x * kHistThreads + threadIdx.x;
+    for (; v + (kHistUnroll - 1) * stride < nvec; v += kHistUnroll * stride) {
+        uint4 r[kHistUnroll];
+#pragma unroll
+        for (int k = 0; k < kHistUnroll; k++)
+            r[k] = ld_stream_u4(vin + v + k * stride);
+#pragma unroll
+        for (int k = 0; k < kHistUnroll; k++)
+            count_vec<BINS, SH>(table, lane4, r[k]);
+    }
+    for (; v < nvec; v += stride)
+        count_vec<BINS, SH>(table, lane4, ld_stream_u4(vin + v));
+    if (blockIdx.x == 0) { // ragged head / tail bytes
+        for (size_t i = threadIdx.x; i < head; i += kHistThreads)
+            atomicAdd(&table[(unsigned)(data[i] >> SH) * 32 + lane], 1u);
+        for (size_t i = tail + threadIdx.x; i < n; i += kHistThreads)
+            atomicAdd(&table[(unsigned)(data[i] >> SH) * 32 + lane], 1u);
+    }
+    __syncthreads();
+
+    // ---- fold the 32 lane columns: warp w owns rows [w*BINS/32, (w+1)*BINS/32) -------------------
+    constexpr int kRowsPerWarp = BINS / 32;
+    unsigned      mine         = 0; // lane r (< kRowsPerWarp) keeps the total of row warp*kRowsPerWarp + r
+#pragma unroll
+    for (int r = 0; r < kRowsPerWarp; r++) {
+        unsigned t = __reduce_add_sync(0xffffffffu, table[(warp * kRowsPerWarp + r) * 32 + lane]);
+        if (lane == r)
+            mine = t;
+    }
+    // ---- cluster merge through DSMEM ---------------------------------------------------------------
+    if (csize > 1)
+        cluster.sync(); // every CTA's `merged` is zeroed before anyone adds remotely
+    unsigned *leader = (csize > 1) ? cluster.map_shared_rank(merged, 0) : merged;
+    if (lane < kRowsPerWarp)
+        atomicAdd(&leader[warp * kRowsPerWarp + lane], mine);
+    if (csize > 1)
+        cluster.sync();
+    else
+        __syncthreads();
+    if (crank != 0)
+        return;
+
+    // ---- leader: one global reduction per bin, last leader publishes --------------------------------
+    unsigned *ticket = scratch;
+    unsigned *acc    = scratch + ((MODE == kHist64) ? kHistAcc64 : kHistAcc256);
+    if (threadIdx.x < BINS)
+        atomicAdd(&acc[threadIdx.x], merged[threadIdx.x]);
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned t = atomicAdd(ticket, 1u);
+        s_last     = (t == gridDim.x / csize - 1);
+    }
+    __syncthreads();
+    if (!s_last)
+        return;
+    __threadfence();
+    if (threadIdx.x < BINS) {
+        unsigned total   = __ldcg(&acc[threadIdx.x]);
+        acc[threadIdx.x] = 0;
+        if (MODE == kHist64) {
+            out64[threadIdx.x] = total;
+        }
+        else {
+            out256[threadIdx.x] = total;
+            if (MODE == kHistFused) {
+                // 4 adjacent 256-bins make one 64-bin
+                unsigned s4 = total + __shfl_xor_sync(0xffffffffu, total, 1);
+                s4 += __shfl_xor_sync(0xffffffffu, s4, 2);
+                if ((threadIdx.x & 3) == 0)
+                    out64[threadIdx.x >> 2] = s4;
+            }
+        }
+    }
+    if (threadIdx.x == 0)
+        *ticket = 0;
+}
+
+static int g_hist_cluster = 2; // CTAs per cluster (1, 2, 4 or 8); 2 packs 148 SMs exactly
+
+template <int MODE>
+static int launch_hist(unsigned *out256, unsigned *out64, const void *d_data, size_t n, cudaStream_t stream)
+{
+    int        st = 0;
+    DeviceCtx *c  = ctx(&st);
+    if (!c)
+        return st;
+    B200_TRY((cudaError_t)ensure(c->hist, kHistWords * sizeof(unsigned), stream));
+    const int cluster = g_hist_cluster;
+    // persistent: one CTA per SM, but never more CTAs than there are 16 KiB slabs of input
+    size_t want = (n / 16 + kHistThreads - 1) / kHistThreads;
+    int    grid = (int)(want < (size_t)c->num_sms ? want : (size_t)c->num_sms);
+    grid        = (grid / cluster) * cluster;
+    if (grid < cluster)
+        grid = cluster;
+
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim            = dim3(grid);
+    cfg.blockDim           = dim3(kHistThreads);
+    cfg.dynamicSmemBytes   = 0;
+    cfg.stream             = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id               = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = cluster;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs              = at;
+    cfg.numAttrs           = 1;
+    B200_TRY(cudaLaunchKernelEx(&cfg, histogram_kernel<MODE>, (const unsigned char *)d_data, n, out256, out64,
+                                (unsigned *)c->hist.ptr));
+    count_launch();
+    return 0;
+}
+
+int set_hist_cluster(int cluster)
+{
+    if (cluster != 1 && cluster != 2 && cluster != 4 && cluster != 8)
+        return (int)cudaErrorInvalidValue;
+    g_hist_cluster = cluster;
+    return 0;
+}
+
+} // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_histogram256_async(uint32_t *d_hist256, const void *d_data, size_t byteCount,
+                                       b200_stream_t stream)
+{
+    return launch_hist<kHist256>(d_hist256, nullptr, d_data, byteCount, (cudaStream_t)stream);
+}
+extern "C" int b200_histogram64_async(uint32_t *d_hist64, const void *d_data, size_t byteCount, b200_stream_t stream)
+{
+    return launch_hist<kHist64>(nullptr, d_hist64, d_data, byteCount, (cudaStream_t)stream);
+}
+extern "C" int b200_histogram_fused_async(uint32_t *d_hist256, uint32_t *d_hist64, const void *d_data,
+                                          size_t byteCount, b200_stream_t stream)
+{
+    return launch_hist<kHistFused>(d_hist256, d_hist64, d_data, byteCount, (cudaStream_t)stream);
+}
+// tuning knob used by bench.py / tests (not part of the stable ABI)
+extern "C" int b200_tune_hist_cluster(int cluster) { return set_hist_cluster(cluster); }

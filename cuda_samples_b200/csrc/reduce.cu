@@ -1,0 +1,228 @@
+// reduce.cu -- single-pass sum reduction for sm_100a.
+//
+// Replaces reduce<T>() and its ten teaching kernels (Samples/2_Concepts_and_Techniques/reduction/
+// reduction_kernel.cu:104-617, launcher :633-982) plus the caller's multi-pass finish
+// (reduction.cpp:292-318) with ONE launch:
+//   * persistent grid (SMs x kCtasPerSm CTAs), grid-stride over 16-byte vectors, kUnroll
+//     independent ld.global.nc.L1::no_allocate.v4 in flight per thread before any arithmetic;
+//   * int: wrapping u32 adds, warp finish with redux.sync (__reduce_add_sync);
+//     float: every batch of 4*kUnroll values is summed as a depth-log2 fp32 tree and then added to
+//     a per-thread fp64 accumulator, so the rounding error does not grow with n;
+//     double: per-thread Kahan (compensated) fp64 accumulators;
+//   * per-CTA partial -> global scratch -> last CTA (atomic ticket + __threadfence) adds the
+//     partials in a fixed order: deterministic run to run, no floating-point atomics;
+//   * d_out[0] = total, d_out[1..out_len) = 0 so every caller path of the sample still adds up.
+// Roofline: HBM-bound, sizeof(T) algorithmic bytes per element (read once, nothing written).
+#include "common.cuh"
+#include "internal.h"
+
+namespace b200 {
+
+constexpr int kReduceThreads = 512;
+constexpr int kReduceCtasPerSm = 3;
+constexpr int kReduceUnroll = 4;
+
+// ---- per-thread accumulators ---------------------------------------------------------------------
+struct LaneI32 {
+    typedef unsigned Part;
+    typedef int      Elem;
+    unsigned s = 0;
+    __device__ __forceinline__ void add_vecs(const uint4 (&v)[kReduceUnroll])
+    {
+#pragma unroll
+        for (int k = 0; k < kReduceUnroll; k++)
+            s += (v[k].x + v[k].y) + (v[k].z + v[k].w);
+    }
+    __device__ __forceinline__ void add_vec(uint4 v) { s += (v.x + v.y) + (v.z + v.w); }
+    __device__ __forceinline__ void add_scalar(int x) { s += (unsigned)x; }
+    __device__ __forceinline__ Part partial() const { return s; }
+};
+
+struct LaneF32 {
+    typedef double Part;
+    typedef float  Elem;
+    double s = 0.0;
+    static __device__ __forceinline__ float sum4(uint4 v)
+    {
+        return (__uint_as_float(v.x) + __uint_as_float(v.y)) + (__uint_as_float(v.z) + __uint_as_float(v.w));
+    }
+    __device__ __forceinline__ void add_vecs(const uint4 (&v)[kReduceUnroll])
+    {
+        float t[kReduceUnroll];
+#pragma unroll
+        for (int k = 0; k < kReduceUnroll; k++)
+            t[k] = sum4(v[k]);
+#pragma unroll
+        for (int w = kReduceUnroll / 2; w >= 1; w >>= 1)
+#pragma unroll
+            for (int k = 0; k < w; k++)
+                t[k] = t[k] + t[k + w];
+        s += (double)t[0];
+    }
+    __device__ __forceinline__ void add_vec(uint4 v) { s += (double)sum4(v); }
+    __device__ __forceinline__ void add_scalar(float x) { s += (double)x; }
+    __device__ __forceinline__ Part partial() const { return s; }
+};
+
+struct LaneF64 {
+    typedef double Part;
+    typedef double Elem;
+    // two Kahan accumulators (one per double of a 16-byte vector)
+    double s0 = 0.0, c0 = 0.0, s1 = 0.0, c1 = 0.0;
+    static __device__ __forceinline__ void kahan(double &s, double &c, double x)
+    {
+        double y = __dsub_rn(x, c);
+        double t = __dadd_rn(s, y);
+        c        = __dsub_rn(__dsub_rn(t, s), y);
+        s        = t;
+    }
+    __device__ __forceinline__ void add_vec(uint4 v)
+    {
+        kahan(s0, c0, __hiloint2double((int)v.y, (int)v.x));
+        kahan(s1, c1, __hiloint2double((int)v.w, (int)v.z));
+    }
+    __device__ __forceinline__ void add_vecs(const uint4 (&v)[kReduceUnroll])
+    {
+#pragma unroll
+        for (int k = 0; k < kReduceUnroll; k++)
+            add_vec(v[k]);
+    }
+    __device__ __forceinline__ void add_scalar(double x) { kahan(s0, c0, x); }
+    __device__ __forceinline__ Part partial() const { return (s0 - c0) + (s1 - c1); }
+};
+
+// ---- CTA-wide sum, fixed order (deterministic) ---------------------------------------------------
+__device__ __forceinline__ unsigned warp_sum(unsigned v) { return __reduce_add_sync(0xffffffffu, v); }
+__device__ __forceinline__ double   warp_sum(double v)
+{
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1)
+        v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+template <typename Part> __device__ __forceinline__ Part block_sum(Part v, Part *smem /* >= 32 */)
+{
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    v = warp_sum(v);
+    if (lane == 0)
+        smem[warp] = v;
+    __syncthreads();
+    Part r = Part(0);
+    if (warp == 0) {
+        r = (lane < (blockDim.x >> 5)) ? smem[lane] : Part(0);
+        r = warp_sum(r);
+    }
+    __syncthreads();
+    return r; // valid in warp 0
+}
+
+// scratch layout: [0] ticket (u32), [16 ..) one 8-byte partial per CTA
+template <typename L>
+__global__ void __launch_bounds__(kReduceThreads, kReduceCtasPerSm)
+    reduce_kernel(const typename L::Elem *__restrict__ in, size_t n, typename L::Elem *__restrict__ out,
+                  size_t out_len, unsigned *__restrict__ ticket, typename L::Part *__restrict__ partials)
+{
+    typedef typename L::Elem Elem;
+    typedef typename L::Part Part;
+    constexpr int kPerVec = 16 / sizeof(Elem);
+    __shared__ Part s_part[32];
+    __shared__ bool s_last;
+
+    L acc;
+    // split [0,n) into scalar head (to 16-byte alignment), vector body, scalar tail
+    const uintptr_t addr = (uintptr_t)in;
+    size_t head = ((16 - (addr & 15)) & 15) / sizeof(Elem);
+    if (head > n)
+        head = n;
+    const size_t nvec = (n - head) / kPerVec;
+    const size_t tail = head + nvec * kPerVec;
+    const uint4 *vin  = reinterpret_cast<const uint4 *>(in + head);
+
+    const size_t stride = (size_t)gridDim.x * kReduceThreads;
+    size_t       v      = (size_t)blockIdx.x * kReduceThreads + threadIdx.x;
+    // main loop: kUnroll independent 16-byte loads in flight per thread
+    for (; v + (kReduceUnroll - 1) * stride < nvec; v += kReduceUnroll * stride) {
+        uint4 r[kReduceUnroll];
+#pragma unroll
+        for (int k = 0; k < kReduceUnroll; k++)
+            r[k] = ld_stream_u4(vin + v + k * stride);
+        acc.add_vecs(r);
+    }
+    for (; v < nvec; v += stride)
+        acc.add_vec(ld_stream_u4(vin + v));
+    if (blockIdx.x == 0) {
+        for (size_t i = threadIdx.x; i < head; i += kReduceThreads)
+            acc.add_scalar(in[i]);
+        for (size_t i = tail + threadIdx.x; i < n; i += kReduceThreads)
+            acc.add_scalar(in[i]);
+    }
+
+    Part p = block_sum<Part>(acc.partial(), s_part);
+    if (threadIdx.x == 0) {
+        partials[blockIdx.x] = p;
+        __threadfence();
+        unsigned t = atomicAdd(ticket, 1u);
+        s_last     = (t == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!s_last)
+        return;
+
+    // last CTA: fixed-order sum of the per-CTA partials
+    __threadfence();
+    Part q = Part(0);
+    for (unsigned i = threadIdx.x; i < gridDim.x; i += kReduceThreads)
+        q += __ldcg(partials + i);
+    q = block_sum<Part>(q, s_part);
+    if (threadIdx.x == 0) {
+        if (out_len > 0)
+            out[0] = (Elem)q;
+        *ticket = 0; // ready for the next call (stream-ordered)
+    }
+    for (size_t i = 1 + threadIdx.x; i < out_len; i += kReduceThreads)
+        out[i] = Elem(0);
+}
+
+template <typename L>
+static int launch_reduce(const typename L::Elem *d_in, size_t n, typename L::Elem *d_out, size_t out_len,
+                         cudaStream_t stream)
+{
+    int        st = 0;
+    DeviceCtx *c  = ctx(&st);
+    if (!c)
+        return st;
+    const int max_grid = c->num_sms * kReduceCtasPerSm;
+    B200_TRY((cudaError_t)ensure(c->reduce, 16 + sizeof(double) * (size_t)max_grid, stream));
+    constexpr int kPerVec = 16 / sizeof(typename L::Elem);
+    size_t        nvec    = n / kPerVec + 1;
+    size_t        want    = (nvec + kReduceThreads - 1) / kReduceThreads;
+    int           grid    = (int)(want < (size_t)max_grid ? want : (size_t)max_grid);
+    if (grid < 1)
+        grid = 1;
+    unsigned *ticket   = reinterpret_cast<unsigned *>(c->reduce.ptr);
+    auto     *partials = reinterpret_cast<typename L::Part *>(reinterpret_cast<char *>(c->reduce.ptr) + 16);
+    reduce_kernel<L><<<grid, kReduceThreads, 0, stream>>>(d_in, n, d_out, out_len, ticket, partials);
+    count_launch();
+    B200_TRY(cudaGetLastError());
+    return 0;
+}
+
+} // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_reduce_i32_async(const int32_t *d_in, size_t n, int32_t *d_out, size_t out_len,
+                                     b200_stream_t stream)
+{
+    return launch_reduce<LaneI32>(d_in, n, d_out, out_len, (cudaStream_t)stream);
+}
+extern "C" int b200_reduce_f32_async(const float *d_in, size_t n, float *d_out, size_t out_len, b200_stream_t stream)
+{
+    return launch_reduce<LaneF32>(d_in, n, d_out, out_len, (cudaStream_t)stream);
+}
+extern "C" int b200_reduce_f64_async(const double *d_in, size_t n, double *d_out, size_t out_len,
+                                     b200_stream_t stream)
+{
+    return launch_reduce<LaneF64>(d_in, n, d_out, out_len, (cudaStream_t)stream);
+}

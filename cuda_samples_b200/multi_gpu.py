@@ -1,0 +1,170 @@
+"""Sharded (one process per GPU) versions of the primitives over torch.distributed / NCCL.
+
+Only the exchange step each primitive really has is a collective:
+  histogram   shard by bytes          -> all_reduce(SUM) of the 256+64 u32 bins (wrap-add is associative:
+                                         bit-exact whatever algorithm NCCL picks)
+  reduce      shard by elements       -> int: all_reduce(SUM) of one i32 (wraps like reduceCPU<int>);
+                                         float/double: all_gather of the G shard sums, added in rank
+                                         order in fp64 on every rank (deterministic, same on all ranks)
+  scan        one long array, contiguous shards -> shard total, all_gather(G x u32), exclusive prefix of
+                                         the lower ranks' totals is this shard's carry, chained scan
+                                         seeded with it (batched scans shard by array: no collective)
+  sort        sample sort             -> all_gather of samples, splitters, local stable partition,
+                                         all_gather of bucket counts, all_to_all of keys and values laid
+                                         out in source-rank order, local stable sort.  Stable globally:
+                                         equal keys share a bucket, sources arrive in rank (= index) order.
+
+The local compute is an injected `ops` object: `CudaOps` (libb200prim.so, the product path) by default.
+The CPU test-suite (gloo, world_size 2) injects a numpy stand-in that lives in tests/ -- there is no
+CPU path in this package.
+"""
+import torch
+import torch.distributed as dist
+
+from . import api
+
+
+class CudaOps:
+    """Local steps on the current CUDA device through the C ABI."""
+
+    device_type = "cuda"
+
+    def histogram_fused(self, data, nbytes):
+        bins = torch.empty(320, dtype=torch.int32, device=data.device)
+        api.histogram_fused(bins[:256], bins[256:], data, nbytes)
+        return bins
+
+    def reduce(self, x, n):
+        out = torch.empty(1, dtype=x.dtype, device=x.device)
+        api.reduce(n, 256, 1, 7, x, out)
+        return out
+
+    def scan_total(self, src, n):
+        tot = torch.empty(1, dtype=torch.int32, device=src.device)
+        api.scan_total(tot, src, n)
+        return tot
+
+    def scan_with_carry(self, dst, src, n, carry):
+        api.scanExclusiveLarge(dst, src, 1, n, d_carry=carry)
+
+    def partition(self, keys, vals, n, splitters, buckets, direction):
+        dk, dv = torch.empty_like(keys), torch.empty_like(vals)
+        counts = torch.empty(buckets, dtype=torch.int32, device=keys.device)
+        api.partition_kv(dk, dv, keys, vals, n, splitters, buckets, direction, counts)
+        return dk, dv, counts
+
+    def sort(self, keys, vals, n, direction):
+        dk, dv = torch.empty_like(keys), torch.empty_like(vals)
+        bk, bv = torch.empty_like(keys), torch.empty_like(vals)
+        api.mergeSort(dk, dv, bk, bv, keys, vals, n, direction)
+        return dk, dv
+
+
+def _world(group=None):
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(group), dist.get_world_size(group)
+    return 0, 1
+
+
+def _u32_as_i64(t):
+    return t.to(torch.int64) & 0xFFFFFFFF
+
+
+# ---------------------------------------------------------------------------------------- histogram
+def histogram_sharded(data, nbytes, ops=None, group=None):
+    """-> (hist256, hist64) of the concatenation of all ranks' shards, on every rank (int32 = u32 bits)."""
+    ops = ops or CudaOps()
+    bins = ops.histogram_fused(data, nbytes)
+    if _world(group)[1] > 1:
+        dist.all_reduce(bins, op=dist.ReduceOp.SUM, group=group)
+    return bins[:256], bins[256:]
+
+
+# ------------------------------------------------------------------------------------------- reduce
+def reduce_sharded(x, n, ops=None, group=None):
+    """-> 1-element tensor with the sum over all shards (same bits on every rank)."""
+    ops = ops or CudaOps()
+    part = ops.reduce(x, n)
+    rank, world = _world(group)
+    if world == 1:
+        return part
+    if part.dtype == torch.int32:
+        dist.all_reduce(part, op=dist.ReduceOp.SUM, group=group)
+        return part
+    parts = torch.empty(world, dtype=part.dtype, device=part.device)
+    dist.all_gather_into_tensor(parts, part, group=group)
+    return parts.to(torch.float64).sum().to(part.dtype).reshape(1)  # fixed rank order
+
+
+# --------------------------------------------------------------------------------------------- scan
+def shard_carry(totals, rank):
+    """Exclusive prefix (mod 2^32) of the shard totals below `rank`; totals: int32 tensor of G u32."""
+    if rank == 0:
+        return torch.zeros(1, dtype=torch.int32, device=totals.device)
+    s = _u32_as_i64(totals[:rank]).sum() & 0xFFFFFFFF
+    s = torch.where(s >= 2**31, s - 2**32, s)
+    return s.to(torch.int32).reshape(1)
+
+
+def scan_sharded(dst, src, n_local, ops=None, group=None):
+    """Exclusive scan of ONE array split into contiguous shards (rank r holds the r-th slice)."""
+    ops = ops or CudaOps()
+    rank, world = _world(group)
+    if world == 1:
+        ops.scan_with_carry(dst, src, n_local, None)
+        return dst
+    total = ops.scan_total(src, n_local)
+    totals = torch.empty(world, dtype=torch.int32, device=total.device)
+    dist.all_gather_into_tensor(totals, total, group=group)
+    ops.scan_with_carry(dst, src, n_local, shard_carry(totals, rank))
+    return dst
+
+
+# --------------------------------------------------------------------------------------------- sort
+def choose_splitters(samples_ordered, world):
+    """samples_ordered: 1-D int64 tensor of ALL ranks' samples in ordered key space (key ^ flip).
+    -> world-1 ascending splitters (int64); bucket(o) = #splitters <= o."""
+    s, _ = torch.sort(samples_ordered)
+    per = s.numel() // world
+    idx = torch.arange(1, world, device=s.device) * per
+    return s[idx]
+
+
+def sort_sharded(keys, vals, n_local, direction=1, ops=None, group=None, samples_per_rank=1024):
+    """Stable global key-value sort.  Rank r ends up with the r-th key range (ascending ranges for
+    direction=1, descending for 0).  -> (keys_out, vals_out, n_out, counts_matrix)."""
+    ops = ops or CudaOps()
+    rank, world = _world(group)
+    if world == 1:
+        dk, dv = ops.sort(keys, vals, n_local, direction)
+        return dk, dv, n_local, None
+    flip = 0 if direction else 0xFFFFFFFF
+    # 1. regular samples of the local keys, in ordered space
+    ns = min(samples_per_rank, max(n_local, 1))
+    step = max(n_local // ns, 1)
+    local = _u32_as_i64(keys[:n_local:step][:ns]) ^ flip
+    if local.numel() < ns:  # tiny shards: pad by repetition so every rank contributes ns samples
+        pad = local[-1:].expand(ns - local.numel()) if local.numel() else torch.zeros(ns, dtype=torch.int64,
+                                                                                    device=keys.device)
+        local = torch.cat([local, pad])
+    gathered = torch.empty(world * ns, dtype=torch.int64, device=keys.device)
+    dist.all_gather_into_tensor(gathered, local.contiguous(), group=group)
+    spl64 = choose_splitters(gathered, world)
+    spl = torch.where(spl64 >= 2**31, spl64 - 2**32, spl64).to(torch.int32).contiguous()
+    # 2. local stable partition into `world` buckets
+    pk, pv, counts = ops.partition(keys, vals, n_local, spl, world, direction)
+    # 3. everyone learns everyone's bucket sizes
+    matrix = torch.empty(world * world, dtype=torch.int32, device=counts.device)
+    dist.all_gather_into_tensor(matrix, counts, group=group)
+    m = matrix.reshape(world, world).cpu()
+    send = m[rank].tolist()
+    recv = m[:, rank].tolist()
+    n_out = int(sum(recv))
+    rk = torch.empty(max(n_out, 1), dtype=keys.dtype, device=keys.device)
+    rv = torch.empty(max(n_out, 1), dtype=vals.dtype, device=vals.device)
+    # 4. all-to-all: the receive buffer is laid out in source-rank order (= original index order)
+    dist.all_to_all_single(rk[:n_out], pk[:n_local], recv, send, group=group)
+    dist.all_to_all_single(rv[:n_out], pv[:n_local], recv, send, group=group)
+    # 5. local stable sort of the received range
+    dk, dv = ops.sort(rk, rv, n_out, direction)
+    return dk, dv, n_out, m

@@ -1,0 +1,106 @@
+/*
+ * b200prim.h -- extended C ABI of libb200prim.so (sm_100a only).
+ *
+ * The drop-in entry points (same names and signatures as the cuda-samples `extern "C"` host
+ * wrappers) are declared in histogram_common.h, scan_common.h, mergeSort_common.h and reduction.h
+ * next to this file.  This header adds what the samples' API cannot express:
+ *   - an explicit stream (the samples launch on the legacy default stream only),
+ *   - size_t lengths (histogram byteCount is `uint` in histogram/histogram_common.h:80-82),
+ *   - status codes instead of exit() (Common/helper_cuda.h:584-616 aborts),
+ *   - host-buffer variants that own the host<->device copies (what a CPU caller of
+ *     histogram256CPU / reduceCPU / scanExclusiveHost / mergeSortHost would switch to),
+ *   - building blocks of the multi-GPU path (shard carry for scan, bucket partition for sort).
+ *
+ * Plain pointers and sizes only.  All `d_*` pointers are device pointers of the CURRENT device,
+ * `h_*` pointers are host pointers (pinned memory gives full PCIe speed; pageable works).
+ * Every function returns 0 on success or a cudaError_t value.  `*_async` functions only enqueue
+ * work on `stream`; they never synchronise.  The library keeps grow-only per-device scratch, so
+ * calls on one device must be stream-ordered with each other (same contract as the samples'
+ * file-static scratch: histogram256.cu:133, scan.cu:182, mergeSort.cu:452).
+ */
+#ifndef B200PRIM_H
+#define B200PRIM_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct CUstream_st *b200_stream_t; /* == cudaStream_t */
+
+/* library / device ---------------------------------------------------------------------------- */
+int         b200_version(void);
+const char *b200_error_string(int status);
+int         b200_device_info(int *num_sms, int *smem_per_block_optin, int *cc_major, int *cc_minor);
+/* number of kernels this library has launched in this process (for bench.py's gpu_launches) */
+unsigned long long b200_launch_count(void);
+/* free all per-device scratch of the current device (the close*() calls do this too) */
+int b200_release_scratch(void);
+
+/* histogram: replaces histogram256()/histogram64() (histogram256.cu:145-155, histogram64.cu:186-200).
+ * d_hist is OVERWRITTEN with u32 counts (wrap mod 2^32); any byteCount >= 0, any alignment.
+ * b200_histogram_fused_async produces both histograms in ONE pass over the data
+ * (hist64[v] = sum of hist256[4v..4v+3], exact: histogram_gold.cpp:41-44 vs :57-60). */
+int b200_histogram256_async(uint32_t *d_hist256, const void *d_data, size_t byteCount, b200_stream_t stream);
+int b200_histogram64_async(uint32_t *d_hist64, const void *d_data, size_t byteCount, b200_stream_t stream);
+int b200_histogram_fused_async(uint32_t *d_hist256, uint32_t *d_hist64, const void *d_data, size_t byteCount,
+                               b200_stream_t stream);
+
+/* reduce: replaces reduce<T>() (reduction_kernel.cu:633-982) + the caller's multi-pass finish
+ * (reduction.cpp:292-318).  Single pass: d_out[0] = sum, d_out[1..out_len) = 0, so callers that
+ * go on to add up `blocks` partials still get the right answer.  int: wrapping 32-bit sum.
+ * float/double: deterministic (fixed grid, fixed-order finish, no floating-point atomics);
+ * |gpu - reduceCPU| <= 1e-5 (fp32) / 1e-12 (fp64) relative. n >= 0 (n == 0 gives 0). */
+int b200_reduce_i32_async(const int32_t *d_in, size_t n, int32_t *d_out, size_t out_len, b200_stream_t stream);
+int b200_reduce_f32_async(const float *d_in, size_t n, float *d_out, size_t out_len, b200_stream_t stream);
+int b200_reduce_f64_async(const double *d_in, size_t n, double *d_out, size_t out_len, b200_stream_t stream);
+
+/* scan: replaces scanExclusiveShort()/scanExclusiveLarge() (scan.cu:210-266): batchSize independent
+ * exclusive +scans of arrayLength u32 each (wrap mod 2^32), single pass, 8 B of traffic per
+ * element.  Any arrayLength >= 1 and any batchSize >= 0 (no power-of-two / size caps).
+ * d_carry (nullable, device pointer to one u32) seeds element 0 of every array: the multi-GPU
+ * path passes the allgathered prefix of the lower shards here.  In place (d_dst == d_src) is fine.
+ * b200_scan_total_async writes sum(d_src[0..n)) mod 2^32 to d_total[0] (the shard total). */
+int b200_scan_exclusive_async(uint32_t *d_dst, const uint32_t *d_src, size_t batchSize, size_t arrayLength,
+                              const uint32_t *d_carry, b200_stream_t stream);
+int b200_scan_total_async(uint32_t *d_total, const uint32_t *d_src, size_t n, b200_stream_t stream);
+
+/* sort: replaces mergeSort() (mergeSort.cu:471-537): STABLE key-value sort, sortDir != 0 ascending,
+ * == 0 descending, ties keep source order.  Result in dst, buf is scratch, src is left untouched.
+ * Any N >= 0 (the sample asserts N % 1024 == 0 and N <= 2^22).  src may not alias dst/buf. */
+int b200_sort_kv_async(uint32_t *d_dstKey, uint32_t *d_dstVal, uint32_t *d_bufKey, uint32_t *d_bufVal,
+                       const uint32_t *d_srcKey, const uint32_t *d_srcVal, size_t N, uint32_t sortDir,
+                       b200_stream_t stream);
+/* stable partition of (key,val) into numBuckets <= 256 buckets by splitters: bucket(k) = number of
+ * splitters s with s <= k (ascending) -- the local step of the multi-GPU sample sort.
+ * d_splitters: numBuckets-1 ascending u32.  d_bucketCounts (numBuckets u32) receives the sizes. */
+int b200_partition_kv_async(uint32_t *d_dstKey, uint32_t *d_dstVal, const uint32_t *d_srcKey,
+                            const uint32_t *d_srcVal, size_t N, const uint32_t *d_splitters, uint32_t numBuckets,
+                            uint32_t sortDir, uint32_t *d_bucketCounts, b200_stream_t stream);
+
+/* counter-based synthetic data, bit-identical to oracle_generate() (oracle/oracle.c): element i of
+ * the stream depends only on (seed, first + i, kind, param), so shards are filled in place. */
+int b200_generate_async(void *d_out, size_t first, size_t n, uint64_t seed, int kind, uint32_t param,
+                        b200_stream_t stream);
+
+/* host-buffer variants: H2D copies, kernels and D2H of the result are all inside the call
+ * (chunked and double-buffered so the copy engine and the SMs overlap); they synchronise before
+ * returning.  These are what bench.py's `e2e` number times. */
+int b200_histogram256_host(uint32_t *h_hist256, const void *h_data, size_t byteCount);
+int b200_histogram64_host(uint32_t *h_hist64, const void *h_data, size_t byteCount);
+int b200_reduce_i32_host(const int32_t *h_in, size_t n, int32_t *h_result);
+int b200_reduce_f32_host(const float *h_in, size_t n, float *h_result);
+int b200_reduce_f64_host(const double *h_in, size_t n, double *h_result);
+int b200_scan_exclusive_host(uint32_t *h_dst, const uint32_t *h_src, size_t batchSize, size_t arrayLength);
+int b200_sort_kv_host(uint32_t *h_dstKey, uint32_t *h_dstVal, const uint32_t *h_srcKey, const uint32_t *h_srcVal,
+                      size_t N, uint32_t sortDir);
+/* pinned host memory for the variants above */
+int b200_host_alloc(void **h_ptr, size_t bytes);
+int b200_host_free(void *h_ptr);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200PRIM_H */

@@ -1,0 +1,517 @@
+"""GPU parity tests (run on a B200: pytest -m gpu).
+
+Every test drives the CUDA path through the C ABI of libb200prim.so (ctypes; torch only provides
+device memory and the stream) and compares it with the oracle (oracle/: CPU restatement of the
+samples' gold code) or with the committed golden vectors produced by the reference's own gold code.
+Bar: bit-exact for histogram / scan / sort / integer reduce; fp32 <= 1e-5, fp64 <= 1e-12 relative
+to the Kahan-summed reduceCPU for floating-point reductions.
+"""
+import ctypes
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+import oracle  # noqa: E402
+
+FP32_RTOL = 1e-5   # BASELINE.json north_star
+FP64_RTOL = 1e-12
+
+
+@pytest.fixture(scope="module")
+def prim():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import cuda_samples_b200 as p
+    info = p.device_info()
+    assert info["cc"][0] == 10, "libb200prim.so is sm_100a only"
+    return p
+
+
+def dev(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def hx(a):
+    return "%016x" % oracle.fnv1a64(a)
+
+
+# ================================================================================== histogram
+def run_hist(prim, data_t, nbytes, which):
+    if which == "256":
+        out = torch.full((256,), -1, dtype=torch.int32).cuda()
+        prim.histogram256(out, data_t, nbytes)
+        return out.cpu().numpy().view(np.uint32)
+    if which == "64":
+        out = torch.full((64,), 12345, dtype=torch.int32).cuda()
+        prim.histogram64(out, data_t, nbytes)
+        return out.cpu().numpy().view(np.uint32)
+    o256 = torch.full((256,), 7, dtype=torch.int32).cuda()
+    o64 = torch.full((64,), 7, dtype=torch.int32).cuda()
+    prim.histogram_fused(o256, o64, data_t, nbytes)
+    return o256.cpu().numpy().view(np.uint32), o64.cpu().numpy().view(np.uint32)
+
+
+def test_histogram_small_golden(prim, golden_small):
+    d = dev(golden_small["hist_in"])
+    assert (run_hist(prim, d, d.numel(), "256") == golden_small["hist256_out"]).all()
+    assert (run_hist(prim, d, d.numel(), "64") == golden_small["hist64_out"]).all()
+    f256, f64 = run_hist(prim, d, d.numel(), "fused")
+    assert (f256 == golden_small["hist256_out"]).all() and (f64 == golden_small["hist64_out"]).all()
+
+
+@pytest.mark.parametrize("nbytes", [0, 1, 3, 4, 15, 16, 17, 4096, 65536 + 5, (1 << 20) + 13, 3 * (1 << 22) + 1])
+def test_histogram_sizes_and_ragged(prim, nbytes):
+    rng = np.random.default_rng(nbytes)
+    h = rng.integers(0, 256, nbytes + 3, dtype=np.uint8)
+    d = dev(h)
+    for offset in (0, 1, 3):  # unaligned starts
+        view = d[offset:offset + nbytes]
+        want256, want64 = oracle.histogram256(h[offset:offset + nbytes]), oracle.histogram64(h[offset:offset + nbytes])
+        assert (run_hist(prim, view, nbytes, "256") == want256).all()
+        assert (run_hist(prim, view, nbytes, "64") == want64).all()
+        f256, f64 = run_hist(prim, view, nbytes, "fused")
+        assert (f256 == want256).all() and (f64 == want64).all()
+
+
+@pytest.mark.parametrize("fill", ["zeros", "ff", "two_values", "ramp"])
+def test_histogram_skewed(prim, fill):
+    n = (8 << 20) + 48
+    if fill == "zeros":
+        h = np.zeros(n, np.uint8)
+    elif fill == "ff":
+        h = np.full(n, 255, np.uint8)
+    elif fill == "two_values":
+        h = np.where(np.arange(n) % 3 == 0, 17, 200).astype(np.uint8)
+    else:
+        h = (np.arange(n) & 255).astype(np.uint8)
+    d = dev(h)
+    assert (run_hist(prim, d, n, "256") == oracle.histogram256(h)).all()
+    assert (run_hist(prim, d, n, "64") == oracle.histogram64(h)).all()
+
+
+def test_histogram_kat_sample_input(prim, kat):
+    """The sample's own input (histogram/main.cpp:92-96): 64 MiB of srand(2009); rand()%256."""
+    n = kat["histogram256"]["bytes"]
+    h = oracle.sample_input("hist_bytes", n, kat["histogram256"]["seed"])
+    d = dev(h)
+    prim.initHistogram256()
+    h256 = run_hist(prim, d, n, "256")
+    assert (int(h256[0]), int(h256[255]), hx(h256)) == (kat["histogram256"]["h0"], kat["histogram256"]["h255"],
+                                                        kat["histogram256"]["fnv"])
+    prim.initHistogram64()
+    h64 = run_hist(prim, d, n, "64")
+    assert (int(h64[0]), int(h64[63]), hx(h64)) == (kat["histogram64"]["h0"], kat["histogram64"]["h63"],
+                                                    kat["histogram64"]["fnv"])
+    # repeated calls overwrite (not accumulate) and stay identical
+    for _ in range(3):
+        assert (run_hist(prim, d, n, "256") == h256).all()
+
+
+@pytest.mark.parametrize("cluster", [1, 2, 4, 8])
+def test_histogram_cluster_sizes(prim, cluster):
+    from cuda_samples_b200._lib import check, lib
+    rng = np.random.default_rng(cluster)
+    h = rng.integers(0, 256, (32 << 20) + 100, dtype=np.uint8)
+    d = dev(h)
+    check(lib.b200_tune_hist_cluster(cluster), "tune")
+    try:
+        assert (run_hist(prim, d, h.size, "256") == oracle.histogram256(h)).all()
+        assert (run_hist(prim, d, 5000, "64") == oracle.histogram64(h[:5000])).all()
+    finally:
+        check(lib.b200_tune_hist_cluster(2), "tune")
+
+
+def test_histogram_dropin_symbols(prim):
+    """The samples' own C entry points (legacy default stream, uint byteCount)."""
+    from cuda_samples_b200._lib import lib
+    rng = np.random.default_rng(3)
+    h = rng.integers(0, 256, 1 << 22, dtype=np.uint8)
+    d = dev(h)
+    out = torch.zeros(256, dtype=torch.int32).cuda()
+    torch.cuda.synchronize()
+    lib.initHistogram256()
+    lib.histogram256(ctypes.c_void_p(out.data_ptr()), ctypes.c_void_p(d.data_ptr()), h.size)
+    torch.cuda.synchronize()
+    assert (out.cpu().numpy().view(np.uint32) == oracle.histogram256(h)).all()
+    lib.initHistogram64()
+    lib.histogram64(ctypes.c_void_p(out.data_ptr()), ctypes.c_void_p(d.data_ptr()), h.size)
+    torch.cuda.synchronize()
+    assert (out[:64].cpu().numpy().view(np.uint32) == oracle.histogram64(h)).all()
+
+
+def test_histogram_large_generated(prim):
+    """1 GiB of generator bytes: the device generator equals the CPU twin and the bins match."""
+    n = 1 << 30
+    d = torch.empty(n, dtype=torch.uint8, device="cuda")
+    prim.generate(d, "bytes", 0, n, 2009)
+    f256, f64 = run_hist(prim, d, n, "fused")
+    assert int(f256.astype(np.uint64).sum()) == n and int(f64.astype(np.uint64).sum()) == n
+    want = np.zeros(256, np.uint64)
+    chunk = 1 << 26
+    for off in range(0, n, chunk):  # CPU regenerates chunk by chunk (counter-based)
+        want += oracle.histogram256(oracle.generate("bytes", off, chunk, 2009))
+    assert (f256 == want.astype(np.uint32)).all()
+    assert (f64 == want.reshape(64, 4).sum(1).astype(np.uint32)).all()
+
+
+# ===================================================================================== reduce
+def run_reduce(prim, x_t, n, blocks=1):
+    out = torch.full((max(blocks, 1),), 77, dtype=x_t.dtype, device="cuda")
+    prim.reduce(n, 256, blocks, 7, x_t, out)
+    return out.cpu().numpy()
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 5, 31, 1023, 4096, (1 << 20) + 3, (1 << 24)])
+def test_reduce_sizes(prim, n):
+    rng = np.random.default_rng(n)
+    xi = rng.integers(-2**31, 2**31, n + 3, dtype=np.int64).astype(np.int32)
+    xf = rng.random(n + 3, dtype=np.float32)
+    xd = rng.random(n + 3, dtype=np.float64)
+    for off in (0, 1, 3):
+        got = run_reduce(prim, dev(xi)[off:off + n], n, 64)
+        assert int(got[0]) == oracle.reduce(xi[off:off + n]) and not got[1:].any()
+        got = run_reduce(prim, dev(xf)[off:off + n], n, 64)
+        want = oracle.reduce(xf[off:off + n])
+        assert abs(float(got[0]) - want) <= FP32_RTOL * abs(want) and not got[1:].any()
+        got = run_reduce(prim, dev(xd)[off:off + n], n, 3)
+        want = oracle.reduce(xd[off:off + n])
+        assert abs(float(got[0]) - want) <= FP64_RTOL * abs(want) and not got[1:].any()
+
+
+def test_reduce_kat_sample_input(prim, kat):
+    """reduction.cpp:483-491 inputs (glibc seed 1): int exact; float/double within the stated tolerance."""
+    for case in kat["reduce"]["cases"]:
+        n = case["n"]
+        got = run_reduce(prim, dev(oracle.sample_input("reduce_i32", n, 1)), n, 64)
+        assert int(got[0]) == case["i32"]
+        got = run_reduce(prim, dev(oracle.sample_input("reduce_f32", n, 1)), n, 64)
+        want = float.fromhex(case["f32_hex"])
+        assert abs(float(got[0]) - want) <= FP32_RTOL * abs(want)
+        got = run_reduce(prim, dev(oracle.sample_input("reduce_f64", n, 1)), n, 64)
+        want = float.fromhex(case["f64_hex"])
+        assert abs(float(got[0]) - want) <= FP64_RTOL * abs(want)
+
+
+def test_reduce_int_wraps_like_reduceCPU(prim):
+    n = 1 << 26
+    x = np.full(n, 0xFF, np.int32)  # 255 * 2^26 > 2^31: wraps negative
+    got = run_reduce(prim, dev(x), n)
+    assert int(got[0]) == oracle.reduce(x) == ((255 << 26) + 2**31) % 2**32 - 2**31
+
+
+def test_reduce_full_size_and_deterministic(prim):
+    """BASELINE config 2: 2^28 elements, int bit-exact, float within tolerance, run-to-run identical."""
+    n = 1 << 28
+    xi = torch.empty(n, dtype=torch.int32, device="cuda")
+    prim.generate(xi, "i32_byte", 0, n, 1)
+    xf = torch.empty(n, dtype=torch.float32, device="cuda")
+    prim.generate(xf, "f32_byte", 0, n, 1)
+    hi = oracle.generate("i32_byte", 0, n, 1)
+    assert (xi[:1 << 20].cpu().numpy() == hi[:1 << 20]).all()
+    got_i = run_reduce(prim, xi, n, 64)
+    assert int(got_i[0]) == oracle.reduce(hi)
+    hf = oracle.generate("f32_byte", 0, n, 1)
+    assert (xf[-(1 << 20):].cpu().numpy() == hf[-(1 << 20):]).all()
+    want = oracle.reduce(hf)
+    got_f = [float(run_reduce(prim, xf, n, 64)[0]) for _ in range(3)]
+    assert abs(got_f[0] - want) <= FP32_RTOL * abs(want)
+    assert got_f[0] == got_f[1] == got_f[2]
+
+
+def test_reduce_dropin_symbols(prim):
+    from cuda_samples_b200._lib import lib
+    n = 1 << 22
+    x = oracle.sample_input("reduce_i32", n, 1)
+    d, out = dev(x), torch.full((64,), 5, dtype=torch.int32).cuda()
+    torch.cuda.synchronize()
+    lib._Z6reduceIiEviiiiPT_S1_(n, 256, 64, 7, ctypes.c_void_p(d.data_ptr()), ctypes.c_void_p(out.data_ptr()))
+    torch.cuda.synchronize()
+    o = out.cpu().numpy()
+    assert int(o.sum()) == oracle.reduce(x) and int(o[0]) == oracle.reduce(x)
+
+
+# ======================================================================================= scan
+def run_scan(prim, src_t, batch, L, short=None, carry=None):
+    dst = torch.full_like(src_t, 0x5A5A5A5A)
+    if short is None:
+        short = L <= prim.MAX_SHORT_ARRAY_SIZE
+    if short and carry is None:
+        prim.scanExclusiveShort(dst, src_t, batch, L)
+    else:
+        prim.scanExclusiveLarge(dst, src_t, batch, L, d_carry=carry)
+    return dst.cpu().numpy().view(np.uint32)
+
+
+def as_i32(a):
+    return np.ascontiguousarray(a).view(np.int32)
+
+
+@pytest.mark.parametrize("L", [4, 32, 1024, 2048, 8192])
+def test_scan_small_golden(prim, golden_small, L):
+    src = golden_small["scan_in"]
+    got = run_scan(prim, dev(as_i32(src)), src.size // L, L)
+    assert (got == golden_small["scan_out_L%d" % L]).all()
+
+
+def test_scan_kat_sample_input(prim, kat):
+    """scan/main.cpp:45-56 input, every array length the sample's two loops visit (hash per length)."""
+    n = kat["scan"]["n"]
+    a = oracle.sample_input("scan_u32", n, kat["scan"]["seed"])
+    d = dev(as_i32(a))
+    prim.initScan()
+    golden = {c["L"]: c for c in kat["scan"]["cases"]}
+    L = prim.MIN_SHORT_ARRAY_SIZE
+    while L <= prim.MAX_LARGE_ARRAY_SIZE:
+        got = run_scan(prim, d, n // L, L)
+        if L in golden:
+            assert int(got[-1]) == golden[L]["last"] and hx(got) == golden[L]["fnv"], L
+        else:
+            assert (got == oracle.scan_exclusive(a, n // L, L)).all(), L
+        L *= 2
+
+
+@pytest.mark.parametrize("batch,L", [(1, 1), (5, 1), (3, 2), (7, 3), (1, 5), (9, 100), (4, 1000), (3, 8191),
+                                     (2, 8193), (3, 20000), (1, 8192 * 33 + 7), (2, 3 * 8192), (1, 1 << 22),
+                                     (16, 1 << 16), (1, (1 << 24) + 4), (0, 16)])
+def test_scan_arbitrary_shapes(prim, batch, L):
+    rng = np.random.default_rng(batch * 1000003 + L)
+    src = rng.integers(0, 2**32, max(batch * L, 1), dtype=np.uint32)[:batch * L]
+    if batch * L == 0:
+        prim.scanExclusiveLarge(torch.empty(4, dtype=torch.int32).cuda(), torch.empty(4, dtype=torch.int32).cuda(),
+                                batch, L)
+        return
+    got = run_scan(prim, dev(as_i32(src)), batch, L, short=False)
+    assert (got == oracle.scan_exclusive(src, batch, L)).all()
+
+
+def test_scan_unaligned_and_in_place(prim):
+    rng = np.random.default_rng(9)
+    src = rng.integers(0, 2**32, (1 << 20) + 8, dtype=np.uint32)
+    d = dev(as_i32(src))
+    for off in (1, 2, 3):
+        n = 1 << 20
+        got = run_scan(prim, d[off:off + n], 1, n, short=False)
+        assert (got == oracle.scan_exclusive(src[off:off + n], 1, n)).all()
+    inplace = d.clone()
+    prim.scanExclusiveLarge(inplace, inplace, 4, 1 << 18)
+    assert (inplace.cpu().numpy().view(np.uint32)[:1 << 20] == oracle.scan_exclusive(src[:1 << 20], 4, 1 << 18)).all()
+
+
+def test_scan_carry_and_total(prim):
+    rng = np.random.default_rng(10)
+    n = (1 << 21) + 12
+    src = rng.integers(0, 2**32, n, dtype=np.uint32)
+    carry = torch.tensor([0x89ABCDEF - 2**32], dtype=torch.int32).cuda()
+    got = run_scan(prim, dev(as_i32(src)), 1, n, carry=carry)
+    assert (got == oracle.scan_exclusive(src, 1, n, 0x89ABCDEF)).all()
+    tot = torch.zeros(1, dtype=torch.int32).cuda()
+    prim.scan_total(tot, dev(as_i32(src)), n)
+    assert int(tot.cpu().numpy().view(np.uint32)[0]) == int(src.astype(np.uint64).sum() % 2**32)
+
+
+def test_scan_full_size(prim):
+    """BASELINE config 3 on one GPU: batch 1, 2^28 u32 (64x the sample's cap), compared element-wise."""
+    n = 1 << 28
+    d = torch.empty(n, dtype=torch.int32, device="cuda")
+    prim.generate(d, "u31", 0, n, 2009)
+    dst = torch.empty_like(d)
+    for _ in range(2):  # second run: descriptors from the first must not leak (epoch)
+        dst.fill_(-1)
+        prim.scanExclusiveLarge(dst, d, 1, n)
+    src = oracle.generate("u31", 0, n, 2009)
+    want = oracle.scan_exclusive(src, 1, n)
+    got = dst.cpu().numpy().view(np.uint32)
+    assert (got == want).all()
+    # the sample's largest legal batched shape as well: 1024 arrays of 262144
+    dst.fill_(-1)
+    prim.scanExclusiveLarge(dst, d, 1024, 262144)
+    assert (dst.cpu().numpy().view(np.uint32) == oracle.scan_exclusive(src, 1024, 262144)).all()
+
+
+def test_scan_dropin_symbols(prim):
+    from cuda_samples_b200._lib import lib
+    rng = np.random.default_rng(12)
+    src = rng.integers(0, 2**32, 1 << 20, dtype=np.uint32)
+    d, out = dev(as_i32(src)), torch.zeros(1 << 20, dtype=torch.int32).cuda()
+    torch.cuda.synchronize()
+    lib.initScan()
+    assert lib.scanExclusiveShort(ctypes.c_void_p(out.data_ptr()), ctypes.c_void_p(d.data_ptr()), 1 << 12, 256) > 0
+    torch.cuda.synchronize()
+    assert (out.cpu().numpy().view(np.uint32) == oracle.scan_exclusive(src, 1 << 12, 256)).all()
+    lib.scanExclusiveLarge(ctypes.c_void_p(out.data_ptr()), ctypes.c_void_p(d.data_ptr()), 4, 262144)
+    torch.cuda.synchronize()
+    assert (out.cpu().numpy().view(np.uint32) == oracle.scan_exclusive(src, 4, 262144)).all()
+
+
+# ======================================================================================= sort
+def run_sort(prim, keys, vals, direction):
+    n = keys.size
+    sk, sv = dev(as_i32(keys)), dev(as_i32(vals))
+    m = max(n, 1)
+    dk, dv = torch.full((m,), -3, dtype=torch.int32).cuda(), torch.full((m,), -3, dtype=torch.int32).cuda()
+    bk, bv = torch.empty(m, dtype=torch.int32).cuda(), torch.empty(m, dtype=torch.int32).cuda()
+    prim.mergeSort(dk, dv, bk, bv, sk, sv, n, direction)
+    # src untouched (mergeSort.cu:502 never writes src)
+    assert (sk.cpu().numpy().view(np.uint32) == keys).all() and (sv.cpu().numpy().view(np.uint32) == vals).all()
+    return dk.cpu().numpy().view(np.uint32)[:n], dv.cpu().numpy().view(np.uint32)[:n]
+
+
+@pytest.mark.parametrize("name", ["d1", "d2", "d3"])
+@pytest.mark.parametrize("direction", [1, 0])
+def test_sort_small_golden(prim, golden_small, name, direction):
+    keys = golden_small["sort_%s_keys" % name]
+    vals = np.arange(keys.size, dtype=np.uint32)
+    gk, gv = run_sort(prim, keys, vals, direction)
+    assert (gk == golden_small["sort_%s_dir%d_msh_keys" % (name, direction)]).all()
+    if name in ("d1", "d2"):  # bit-exact vs the reference's mergeSortHost where it is stable
+        assert (gv == golden_small["sort_%s_dir%d_msh_vals" % (name, direction)]).all()
+    sk, sv = oracle.stable_sort_kv(keys, vals, direction)
+    assert (gk == sk).all() and (gv == sv).all()
+
+
+@pytest.mark.parametrize("n", [0, 1, 2, 33, 1000, 1024, 8191, 8192, 8193, 100000, (1 << 20) + 77])
+@pytest.mark.parametrize("direction", [1, 0])
+def test_sort_sizes(prim, n, direction):
+    rng = np.random.default_rng(n + direction)
+    for keys in (rng.integers(0, 2**32, n, dtype=np.uint32), rng.integers(0, 7, n, dtype=np.uint32),
+                 np.full(n, 0xFFFFFFFF, np.uint32), np.zeros(n, np.uint32)):
+        vals = rng.integers(0, 2**32, n, dtype=np.uint32)
+        gk, gv = run_sort(prim, keys, vals, direction)
+        sk, sv = oracle.stable_sort_kv(keys, vals, direction)
+        assert (gk == sk).all() and (gv == sv).all()
+
+
+def test_sort_kat_sample_input(prim, kat):
+    """mergeSort/main.cpp:46-71: N = 4 Mi, srand(2009); rand()%65536, val = i, ascending."""
+    m = kat["mergeSort"]
+    keys = oracle.sample_input("sort_keys", m["n"], m["seed"])
+    vals = oracle.fill_values(m["n"])
+    prim.initMergeSort()
+    gk, gv = run_sort(prim, keys, vals, m["dir"])
+    assert hx(gk) == m["stable"]["fnv_keys"] and hx(gv) == m["stable"]["fnv_vals"]
+    # the sample's own acceptance test
+    assert oracle.validate_sorted_keys(gk, keys, 65536, 1) == 1
+    assert oracle.validate_sorted_values(gk, gv, keys) == (1, 1)
+    if oracle.ref is not None:
+        assert oracle.ref.validate_sorted_keys(gk, keys, 65536, 1) == 1
+        assert oracle.ref.validate_sorted_values(gk, gv, keys) == 1
+
+
+@pytest.mark.parametrize("dataset", ["d1", "d2"])
+def test_sort_matches_mergeSortHost_where_it_is_stable(prim, dataset):
+    n = 1 << 20
+    if dataset == "d1":
+        keys = oracle.generate("key_unique", 0, n, 5)
+    else:
+        keys = oracle.generate("key_tile_unique", 0, n, 0, 1 << 12)  # each key 256 times, unique per tile
+    vals = oracle.fill_values(n)
+    for direction in (1, 0):
+        gk, gv = run_sort(prim, keys, vals, direction)
+        mk, mv = oracle.merge_sort_host(keys, vals, direction)
+        assert (gk == mk).all() and (gv == mv).all()
+
+
+def test_sort_full_size_properties(prim):
+    """BASELINE config 5 on one GPU: 2^28 pairs; checked through size-independent properties on the GPU
+    (sortedness, key/value pairing, stability, multiset through the value permutation)."""
+    n = 1 << 28
+    sk = torch.empty(n, dtype=torch.int32, device="cuda")
+    sv = torch.arange(n, dtype=torch.int32, device="cuda")
+    dk, dv, bk, bv = (torch.empty(n, dtype=torch.int32, device="cuda") for _ in range(4))
+    for kind, param, direction in (("key_unique", 0, 1), ("key_tile_unique", 1 << 20, 1), ("key_mod", 65536, 0)):
+        prim.generate(sk, kind, 0, n, 2009, param)
+        prim.mergeSort(dk, dv, bk, bv, sk, sv, n, direction)
+        ku = dk.to(torch.int64) & 0xFFFFFFFF
+        ordered = (ku[1:] >= ku[:-1]) if direction else (ku[1:] <= ku[:-1])
+        assert bool(ordered.all())
+        ties = ku[1:] == ku[:-1]
+        assert bool((dv[1:][ties] > dv[:-1][ties]).all())          # stable: ties keep source order
+        assert bool((sk[dv.to(torch.int64)] == dk).all())           # pairing: resKey[j] == srcKey[resVal[j]]
+        seen = torch.zeros(n, dtype=torch.bool, device="cuda")
+        seen[dv.to(torch.int64)] = True
+        assert bool(seen.all())                                    # values are a permutation of 0..n-1
+        del ku, ordered, ties, seen
+
+
+def test_sort_dropin_symbols(prim):
+    from cuda_samples_b200._lib import lib
+    n = 1 << 18
+    keys = oracle.sample_input("sort_keys", n, 2009)
+    vals = oracle.fill_values(n)
+    t = [dev(as_i32(keys)), dev(as_i32(vals))] + [torch.zeros(n, dtype=torch.int32).cuda() for _ in range(4)]
+    sk, sv, bk, bv, dk, dv = [ctypes.c_void_p(x.data_ptr()) for x in t]
+    torch.cuda.synchronize()
+    lib.initMergeSort()
+    lib.mergeSort(dk, dv, bk, bv, sk, sv, n, 1)
+    torch.cuda.synchronize()
+    wk, wv = oracle.stable_sort_kv(keys, vals, 1)
+    assert (t[4].cpu().numpy().view(np.uint32) == wk).all() and (t[5].cpu().numpy().view(np.uint32) == wv).all()
+
+
+@pytest.mark.parametrize("buckets", [1, 2, 8, 256])
+@pytest.mark.parametrize("direction", [1, 0])
+def test_partition_kv(prim, buckets, direction):
+    rng = np.random.default_rng(buckets)
+    n = 300000
+    keys = rng.integers(0, 2**32, n, dtype=np.uint32)
+    keys[::7] = keys[0]
+    vals = np.arange(n, dtype=np.uint32)
+    flip = np.uint32(0 if direction else 0xFFFFFFFF)
+    spl = np.sort(rng.integers(0, 2**32, buckets - 1, dtype=np.uint32))
+    if buckets > 2:
+        spl[1] = spl[0]  # an empty bucket
+    dk, dv = torch.empty(n, dtype=torch.int32).cuda(), torch.empty(n, dtype=torch.int32).cuda()
+    counts = torch.full((buckets,), -1, dtype=torch.int32).cuda()
+    d_spl = dev(as_i32(spl)) if buckets > 1 else torch.zeros(1, dtype=torch.int32).cuda()
+    prim.partition_kv(dk, dv, dev(as_i32(keys)), dev(as_i32(vals)), n, d_spl, buckets, direction, counts)
+    b = np.searchsorted(spl, keys ^ flip, side="right")
+    order = np.argsort(b, kind="stable")
+    assert (counts.cpu().numpy() == np.bincount(b, minlength=buckets)).all()
+    assert (dk.cpu().numpy().view(np.uint32) == keys[order]).all()
+    assert (dv.cpu().numpy().view(np.uint32) == vals[order]).all()
+
+
+# ================================================================================== generator
+@pytest.mark.parametrize("kind,param,dtype", [("bytes", 0, torch.uint8), ("u31", 0, torch.int32),
+                                              ("i32_byte", 0, torch.int32), ("f32_byte", 0, torch.float32),
+                                              ("key_unique", 0, torch.int32), ("key_tile_unique", 4096, torch.int32),
+                                              ("key_mod", 65536, torch.int32), ("f64_byte", 0, torch.float64)])
+def test_generator_matches_cpu_twin(prim, kind, param, dtype):
+    n, first = 100003, 12345678901
+    d = torch.empty(n, dtype=dtype, device="cuda")
+    prim.generate(d, kind, first, n, 2009, param)
+    want = oracle.generate(kind, first, n, 2009, param)
+    assert d.cpu().numpy().tobytes() == want.tobytes()
+
+
+# ====================================================================== host-buffer (e2e) variants
+def test_host_variants(prim):
+    rng = np.random.default_rng(77)
+    n = (80 << 20) + 1234  # > 2 staging chunks
+    hb = rng.integers(0, 256, n, dtype=np.uint8)
+    assert (prim.histogram256_host(hb) == oracle.histogram256(hb)).all()
+    assert (prim.histogram64_host(hb) == oracle.histogram64(hb)).all()
+    xi = rng.integers(-2**31, 2**31, n // 4, dtype=np.int64).astype(np.int32)
+    assert prim.reduce_host(xi) == oracle.reduce(xi)
+    xf = rng.random(n // 4, dtype=np.float32)
+    want = oracle.reduce(xf)
+    assert abs(prim.reduce_host(xf) - want) <= FP32_RTOL * abs(want)
+    xd = rng.random(n // 8, dtype=np.float64)
+    want = oracle.reduce(xd)
+    assert abs(prim.reduce_host(xd) - want) <= FP64_RTOL * abs(want)
+    src = rng.integers(0, 2**32, n // 4, dtype=np.uint32)
+    dst = np.empty_like(src)
+    for batch, L in ((1, src.size), (src.size // 1024, 1024), (2, src.size // 2)):
+        m = batch * L
+        prim.scan_exclusive_host(dst, src, batch, L)
+        assert (dst[:m] == oracle.scan_exclusive(src[:m], batch, L)).all(), (batch, L)
+    keys = rng.integers(0, 1000, 1 << 21, dtype=np.uint32)
+    vals = np.arange(keys.size, dtype=np.uint32)
+    ok, ov = np.empty_like(keys), np.empty_like(vals)
+    for direction in (1, 0):
+        prim.sort_kv_host(ok, ov, keys, vals, keys.size, direction)
+        wk, wv = oracle.stable_sort_kv(keys, vals, direction)
+        assert (ok == wk).all() and (ov == wv).all()
