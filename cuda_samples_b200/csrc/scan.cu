@@ -226,7 +226,7 @@ __global__ void __launch_bounds__(kScanThreads)
             else {
                 if (lane == 0)
                     st_relaxed_u64(desc + tile, make_desc(epoch, kStA, aggregate));
-                prefix += look_back(desc, tile, first_tile, epoch);
+                prefix = look_back(desc, tile, first_tile, epoch); // the first tile's prefix already holds the carry
                 if (lane == 0)
                     st_relaxed_u64(desc + tile, make_desc(epoch, kStP, prefix + aggregate));
             }
