@@ -43,6 +43,9 @@ SIGNATURES = {
     "b200_host_alloc": (ci, [ctypes.POINTER(vp), sz]),
     "b200_host_free": (ci, [vp]),
     "b200_tune_hist_cluster": (ci, [ci]),
+    "b200_tune_scan_tma": (ci, [ci]),
+    "b200_tune_scan_window": (ci, [ci]),
+    "b200_tune_sort_lookback": (ci, [ci]),
     # drop-in entry points (the samples' own signatures)
     "initHistogram64": (None, []), "closeHistogram64": (None, []), "histogram64": (None, [vp, vp, u32]),
     "initHistogram256": (None, []), "closeHistogram256": (None, []), "histogram256": (None, [vp, vp, u32]),

@@ -33,8 +33,10 @@ constexpr unsigned kDescA = 1u << 30, kDescP = 2u << 30, kDescValue = (1u << 30)
 
 // shared memory of the pass kernel (dynamic, > 48 KiB)
 struct SortSmem {
-    unsigned buf[kSortTile];              // keys, then values, in digit order
-    unsigned whist[kSortWarps][kRadix];   // warp-private digit counters -> per-warp scatter bases
+    unsigned buf[kSortTile];              // keys in digit order
+    unsigned vbuf[kSortTile];             // values in digit order
+    uint2    wc[kSortWarps][kRadix];      // per warp and digit: {lane mask of the current item, running count}
+                                          // -> .y becomes the warp's scatter base for the digit
     unsigned gofs[kRadix];                // global index of a digit's first slot minus its tile-local start
     unsigned wsum[kRadix / 32];
     unsigned splitters[kRadix];
@@ -47,9 +49,9 @@ template <bool kBucket> struct DigitOp {
     const unsigned *spl; // shared memory
     __device__ __forceinline__ unsigned operator()(unsigned key) const
     {
-        const unsigned o = key ^ flip;
         if (!kBucket)
-            return (o >> shift) & 255u;
+            return ((key >> shift) ^ flip) & 255u; // shift + one LOP3
+        const unsigned o = key ^ flip;
         // number of splitters <= o  (upper bound), nspl <= 255
         unsigned lo = 0, hi = nspl;
         while (lo < hi) {
@@ -63,7 +65,14 @@ template <bool kBucket> struct DigitOp {
     }
 };
 
-// lanes of the warp holding the same 8-bit digit (ballot per bit)
+__device__ __forceinline__ uint2 lds_u2(const uint2 *p)
+{
+    uint2 r;
+    asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "r"(smem_u32(p)) : "memory");
+    return r;
+}
+
+// lanes of the warp holding the same 8-bit digit (ballot per bit) -- kept for reference / the micro-benchmark
 __device__ __forceinline__ unsigned match_digit(unsigned d)
 {
     unsigned mask = 0xffffffffu;
@@ -74,6 +83,40 @@ __device__ __forceinline__ unsigned match_digit(unsigned d)
         mask &= bit ? vote : ~vote;
     }
     return mask;
+}
+
+// Last CTA of a histogram kernel: warp p turns histogram p (256 counts) into exclusive offsets in place
+// (lane l owns entries [8l, 8l+8)); optionally copies the first nspl+1 raw counts out first.
+__device__ __forceinline__ void finish_digit_offsets(unsigned *ghist, int passes, unsigned *counts_out, unsigned nspl)
+{
+    const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if ((int)warp < passes) {
+        unsigned *g = ghist + warp * kRadix + lane * 8;
+        unsigned  c[8], sum = 0;
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            c[i] = __ldcg(g + i);
+            sum += c[i];
+        }
+        if (counts_out)
+#pragma unroll
+            for (int i = 0; i < 8; i++)
+                if (lane * 8 + i <= nspl)
+                    counts_out[lane * 8 + i] = c[i];
+        unsigned inc = sum;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            unsigned t = __shfl_up_sync(0xffffffffu, inc, d);
+            if (lane >= d)
+                inc += t;
+        }
+        unsigned run = inc - sum;
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            g[i] = run;
+            run += c[i];
+        }
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -146,43 +189,107 @@ __global__ void __launch_bounds__(kSortThreads)
     if (!s_last)
         return;
     __threadfence();
-    // warp p scans histogram p: lane l owns entries [8l, 8l+8)
-    const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (warp < P) {
-        unsigned *g = ghist + warp * kRadix + lane * 8;
-        unsigned  c[8], sum = 0;
+    finish_digit_offsets(ghist, P, kBucket ? counts_out : nullptr, nspl);
+    if (threadIdx.x == 0)
+        *ticket = 0;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Radix case of the above with the byte-histogram technique of histogram.cu: four [bin][lane] tables
+// (one per key byte, 128 KiB of shared memory), lane l only touches column l -> every shared atomic
+// is bank-conflict-free whatever the key distribution.  One CTA of 1024 threads per SM.
+// ---------------------------------------------------------------------------------------------------
+constexpr int kHist4Threads = 1024;
+
+__global__ void __launch_bounds__(kHist4Threads, 1)
+    sort_hist4_kernel(const unsigned *__restrict__ keys, size_t n, unsigned flip, unsigned *__restrict__ ghist,
+                      unsigned *__restrict__ ticket)
+{
+    extern __shared__ __align__(16) unsigned tab[]; // [4][256][32]
+    __shared__ bool s_last;
+    const unsigned  lane = threadIdx.x & 31, warp = threadIdx.x >> 5, lane4 = lane * 4;
+    for (int i = threadIdx.x; i < 4 * kRadix * 32; i += kHist4Threads)
+        tab[i] = 0;
+    __syncthreads();
+    char *base = reinterpret_cast<char *>(tab);
+    auto  count = [&](unsigned key) {
+        const unsigned o = key ^ flip;
+        atomicAdd(reinterpret_cast<unsigned *>(base + (((o << 7) & 0x7F80u) | lane4)), 1u);
+        atomicAdd(reinterpret_cast<unsigned *>(base + 32768 + (((o >> 1) & 0x7F80u) | lane4)), 1u);
+        atomicAdd(reinterpret_cast<unsigned *>(base + 65536 + (((o >> 9) & 0x7F80u) | lane4)), 1u);
+        atomicAdd(reinterpret_cast<unsigned *>(base + 98304 + (((o >> 17) & 0x7F80u) | lane4)), 1u);
+    };
+    const uintptr_t addr = (uintptr_t)keys;
+    size_t          head = ((16 - (addr & 15)) & 15) / 4;
+    if (head > n)
+        head = n;
+    const size_t nvec   = (n - head) / 4;
+    const size_t tail   = head + nvec * 4;
+    const uint4 *vin    = reinterpret_cast<const uint4 *>(keys + head);
+    const size_t stride = (size_t)gridDim.x * kHist4Threads;
+    size_t       v      = (size_t)blockIdx.x * kHist4Threads + threadIdx.x;
+    for (; v + 3 * stride < nvec; v += 4 * stride) {
+        uint4 r[4];
 #pragma unroll
-        for (int i = 0; i < 8; i++) {
-            c[i] = __ldcg(g + i);
-            sum += c[i];
-        }
-        if (kBucket && counts_out)
+        for (int k = 0; k < 4; k++)
+            r[k] = ld_stream_u4(vin + v + k * stride);
 #pragma unroll
-            for (int i = 0; i < 8; i++)
-                if (lane * 8 + i <= nspl)
-                    counts_out[lane * 8 + i] = c[i];
-        unsigned inc = sum;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            unsigned t = __shfl_up_sync(0xffffffffu, inc, d);
-            if (lane >= d)
-                inc += t;
-        }
-        unsigned run = inc - sum;
-#pragma unroll
-        for (int i = 0; i < 8; i++) {
-            g[i] = run;
-            run += c[i];
+        for (int k = 0; k < 4; k++) {
+            count(r[k].x);
+            count(r[k].y);
+            count(r[k].z);
+            count(r[k].w);
         }
     }
+    for (; v < nvec; v += stride) {
+        uint4 r = ld_stream_u4(vin + v);
+        count(r.x);
+        count(r.y);
+        count(r.z);
+        count(r.w);
+    }
+    if (blockIdx.x == 0) {
+        for (size_t i = threadIdx.x; i < head; i += kHist4Threads)
+            count(keys[i]);
+        for (size_t i = tail + threadIdx.x; i < n; i += kHist4Threads)
+            count(keys[i]);
+    }
+    __syncthreads();
+    // fold the lane columns: 1024 rows, 32 per warp; lane r keeps row warp*32 + r
+    unsigned mine = 0;
+#pragma unroll 8
+    for (int r = 0; r < 32; r++) {
+        unsigned t = __reduce_add_sync(0xffffffffu, tab[(warp * 32 + r) * 32 + lane]);
+        if ((int)lane == r)
+            mine = t;
+    }
+    if (mine)
+        atomicAdd(&ghist[warp * 32 + lane], mine);
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned t = atomicAdd(ticket, 1u);
+        s_last     = (t == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!s_last)
+        return;
+    __threadfence();
+    finish_digit_offsets(ghist, 4, nullptr, 0);
     if (threadIdx.x == 0)
         *ticket = 0;
 }
 
 // ---------------------------------------------------------------------------------------------------
 // One scatter pass (chained scan over tiles).
+// Ranking inside a warp: per item, every lane ORs its lane bit into a warp-private shared word of its
+// digit (one ATOMS.OR), reads the word back -> the lanes holding the same digit, and the running
+// count of that digit kept next to it (one 64-bit shared load fetches both).  rank = count + number
+// of lower lanes in the mask; the lowest lane of each group writes {0, count + group size} back.
+// Measured on B200 (profiles/microbench/match_bench.cu): 3.4x cheaper than eight ballots and 8.4x
+// cheaper than MATCH.ANY.  Index order inside the tile = (warp, item, lane), so ranks are stable.
 // ---------------------------------------------------------------------------------------------------
-template <bool kBucket>
+template <bool kBucket, int kLB>
 __global__ void __launch_bounds__(kSortThreads, 2)
     sort_pass_kernel(const unsigned *__restrict__ kin, const unsigned *__restrict__ vin, unsigned *__restrict__ kout,
                      unsigned *__restrict__ vout, unsigned n, unsigned shift, unsigned flip,
@@ -192,24 +299,26 @@ __global__ void __launch_bounds__(kSortThreads, 2)
     extern __shared__ __align__(16) unsigned char smem_raw[];
     SortSmem      &S    = *reinterpret_cast<SortSmem *>(smem_raw);
     const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const unsigned lt = lanemask_lt();
 
     if (tid == 0)
         S.tile = atomicAdd(ticket, 1u);
     for (int i = tid; i < kSortWarps * kRadix; i += kSortThreads)
-        (&S.whist[0][0])[i] = 0;
+        (&S.wc[0][0])[i] = make_uint2(0u, 0u);
     if (kBucket && tid < nspl)
         S.splitters[tid] = splitters[tid];
     __syncthreads();
     const unsigned   tile  = S.tile;
     const unsigned   base  = tile * kSortTile;
     const unsigned   valid = (n - base < kSortTile) ? (n - base) : kSortTile;
+    const bool       full  = valid == kSortTile;
     DigitOp<kBucket> op{shift, flip, nspl, S.splitters};
 
     // ---- load keys (warp-striped: item i of lane l is element warp*512 + i*32 + l of the tile) --------
     unsigned       key[kSortItems];
     const unsigned wbase = warp * (kSortItems * 32) + lane;
     const unsigned pad   = ~flip; // (pad ^ flip) = 0xffffffff: last digit in every pass, ranks after all valid keys
-    if (valid == kSortTile) {
+    if (full) {
 #pragma unroll
         for (int i = 0; i < kSortItems; i++)
             key[i] = __ldg(kin + base + wbase + i * 32);
@@ -222,24 +331,24 @@ __global__ void __launch_bounds__(kSortThreads, 2)
 
     // ---- rank inside the warp, in index order -----------------------------------------------------------
     unsigned rank[kSortItems];
+    uint2   *mywc = S.wc[warp];
 #pragma unroll
     for (int i = 0; i < kSortItems; i++) {
-        const unsigned d      = op(key[i]);
-        const unsigned mask   = match_digit(d);
-        const unsigned leader = __ffs(mask) - 1;
-        unsigned       pre    = 0;
-        if (lane == leader) {
-            pre              = S.whist[warp][d];
-            S.whist[warp][d] = pre + __popc(mask);
-        }
-        pre     = __shfl_sync(0xffffffffu, pre, leader);
-        rank[i] = pre + __popc(mask & lanemask_lt());
+        uint2 *slot = mywc + op(key[i]);
+        atomicOr(&slot->x, 1u << lane);
+        __syncwarp();
+        const uint2    w     = lds_u2(slot); // {lanes with this digit, count so far}
+        const unsigned below = w.x & lt;
+        rank[i]              = w.y + __popc(below);
+        __syncwarp();
+        if (below == 0) // lowest lane of the group: clear the mask, advance the count
+            *slot = make_uint2(0u, w.y + __popc(w.x));
         __syncwarp();
     }
 
     // values: issue the loads now, they are consumed after the look-back
     unsigned val[kSortItems];
-    if (valid == kSortTile) {
+    if (full) {
 #pragma unroll
         for (int i = 0; i < kSortItems; i++)
             val[i] = __ldg(vin + base + wbase + i * 32);
@@ -256,8 +365,8 @@ __global__ void __launch_bounds__(kSortThreads, 2)
     if (tid < kRadix) {
 #pragma unroll
         for (int w = 0; w < kSortWarps; w++) {
-            unsigned t       = S.whist[w][tid];
-            S.whist[w][tid]  = count;
+            unsigned t     = S.wc[w][tid].y;
+            S.wc[w][tid].y = count;
             count += t;
         }
         st_relaxed_u32(desc + (size_t)tile * kRadix + tid, (tile == 0 ? kDescP : kDescA) | count);
@@ -282,18 +391,27 @@ __global__ void __launch_bounds__(kSortThreads, 2)
         tile_start += woff;
 #pragma unroll
         for (int w = 0; w < kSortWarps; w++)
-            S.whist[w][tid] += tile_start;
+            S.wc[w][tid].y += tile_start;
         unsigned excl = 0;
         if (tile > 0) {
+            // thread d walks back over the earlier tiles' counts of digit d.  kLB descriptors are fetched
+            // per round trip (independent loads), then consumed nearest-first.
             const unsigned *dp = desc + tid;
-            for (long long t = (long long)tile - 1;; t--) {
-                unsigned d;
-                do {
-                    d = ld_relaxed_u32(dp + (size_t)t * kRadix);
-                } while ((d >> 30) == 0);
-                excl += d & kDescValue;
-                if (d & kDescP)
-                    break;
+            long long       t  = (long long)tile - 1;
+            bool            done = false;
+            while (!done) {
+                unsigned d[kLB];
+#pragma unroll
+                for (int j = 0; j < kLB; j++)
+                    d[j] = (t - j >= 0) ? ld_relaxed_u32(dp + (size_t)(t - j) * kRadix) : kDescP;
+#pragma unroll
+                for (int j = 0; j < kLB; j++) {
+                    if (done || (d[j] >> 30) == 0)
+                        break; // not published yet: poll again from this tile
+                    excl += d[j] & kDescValue;
+                    t--;
+                    done = (d[j] & kDescP) != 0;
+                }
             }
             st_relaxed_u32(desc + (size_t)tile * kRadix + tid, kDescP | (excl + count));
         }
@@ -301,35 +419,35 @@ __global__ void __launch_bounds__(kSortThreads, 2)
     }
     __syncthreads();
 
-    // ---- keys: to shared memory in digit order, then out -----------------------------------------------
+    // ---- keys and values: to shared memory in digit order, then out as contiguous runs per digit ----------
 #pragma unroll
     for (int i = 0; i < kSortItems; i++) {
-        const unsigned d = op(key[i]);
-        rank[i] += S.whist[warp][d]; // tile-local slot
-        S.buf[rank[i]] = key[i];
+        const unsigned slot = rank[i] + mywc[op(key[i])].y; // tile-local position
+        S.buf[slot]         = key[i];
+        S.vbuf[slot]        = val[i];
     }
     __syncthreads();
-    unsigned gidx[kSortItems];
+    if (full) {
 #pragma unroll
-    for (int k = 0; k < kSortItems; k++) {
-        const unsigned j = tid + k * kSortThreads;
-        const unsigned x = S.buf[j];
-        const unsigned d = op(x);
-        gidx[k]          = S.gofs[d] + j;
-        if (j < valid)
-            kout[gidx[k]] = x;
+        for (int k = 0; k < kSortItems; k++) {
+            const unsigned j = tid + k * kSortThreads;
+            const unsigned x = S.buf[j];
+            const unsigned g = S.gofs[op(x)] + j;
+            kout[g]          = x;
+            vout[g]          = S.vbuf[j];
+        }
     }
-    __syncthreads();
-    // ---- values: same slots ------------------------------------------------------------------------------
+    else {
 #pragma unroll
-    for (int i = 0; i < kSortItems; i++)
-        S.buf[rank[i]] = val[i];
-    __syncthreads();
-#pragma unroll
-    for (int k = 0; k < kSortItems; k++) {
-        const unsigned j = tid + k * kSortThreads;
-        if (j < valid)
-            vout[gidx[k]] = S.buf[j];
+        for (int k = 0; k < kSortItems; k++) {
+            const unsigned j = tid + k * kSortThreads;
+            const unsigned x = S.buf[j];
+            const unsigned g = S.gofs[op(x)] + j;
+            if (j < valid) {
+                kout[g] = x;
+                vout[g] = S.vbuf[j];
+            }
+        }
     }
 }
 
@@ -337,15 +455,31 @@ __global__ void __launch_bounds__(kSortThreads, 2)
 //                         | [4112, 4128) pass tickets | descriptors [passes][tiles][256] from 4128
 constexpr size_t kSortOffHist = 16, kSortOffTickets = 16 + 4 * kRadix * 4, kSortOffDesc = kSortOffTickets + 16;
 
-template <bool kBucket> static int prepare_pass_kernel()
+static int g_sort_lb = 4; // look-back descriptors fetched per round trip (1, 4 or 8)
+
+template <bool kBucket, int kLB>
+static int launch_pass(unsigned tiles, cudaStream_t stream, const unsigned *kin, const unsigned *vin, unsigned *kout,
+                       unsigned *vout, unsigned n, unsigned shift, unsigned flip, const unsigned *spl, unsigned nspl,
+                       const unsigned *gbase, unsigned *ticket, unsigned *desc)
 {
     static bool done = false;
     if (!done) {
-        B200_TRY(cudaFuncSetAttribute(sort_pass_kernel<kBucket>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        B200_TRY(cudaFuncSetAttribute(sort_pass_kernel<kBucket, kLB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)sizeof(SortSmem)));
         done = true;
     }
-    return 0;
+    sort_pass_kernel<kBucket, kLB><<<tiles, kSortThreads, sizeof(SortSmem), stream>>>(
+        kin, vin, kout, vout, n, shift, flip, spl, nspl, gbase, ticket, desc);
+    return (int)cudaGetLastError();
+}
+
+template <bool kBucket, typename... Args> static int launch_pass_lb(Args... args)
+{
+    if (g_sort_lb <= 1)
+        return launch_pass<kBucket, 1>(args...);
+    if (g_sort_lb <= 4)
+        return launch_pass<kBucket, 4>(args...);
+    return launch_pass<kBucket, 8>(args...);
 }
 
 } // namespace b200
@@ -365,7 +499,6 @@ extern "C" int b200_sort_kv_async(uint32_t *d_dstKey, uint32_t *d_dstVal, uint32
     DeviceCtx *c  = ctx(&st);
     if (!c)
         return st;
-    B200_TRY((cudaError_t)prepare_pass_kernel<false>());
     const unsigned tiles      = (unsigned)((N + kSortTile - 1) / kSortTile);
     const size_t   desc_bytes = (size_t)tiles * kRadix * 4;
     const size_t   need       = kSortOffDesc + 4 * desc_bytes;
@@ -377,22 +510,29 @@ extern "C" int b200_sort_kv_async(uint32_t *d_dstKey, uint32_t *d_dstVal, uint32
     unsigned *tickets = reinterpret_cast<unsigned *>(base + kSortOffTickets);
     const unsigned flip = sortDir ? 0u : 0xffffffffu;
 
-    size_t want = (N / 4 + kSortThreads - 1) / kSortThreads;
-    size_t cap  = (size_t)c->num_sms * 4;
-    int    grid = (int)(want < cap ? want : cap);
-    if (grid < 1)
-        grid = 1;
-    sort_hist_kernel<false><<<grid, kSortThreads, 0, stream>>>(d_srcKey, N, flip, nullptr, 0, ghist, hticket, nullptr);
-    B200_TRY(cudaGetLastError());
+    {
+        static bool prepared = false;
+        if (!prepared) {
+            B200_TRY(cudaFuncSetAttribute(sort_hist4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          4 * kRadix * 32 * 4));
+            prepared = true;
+        }
+        size_t want = (N / 4 + kHist4Threads - 1) / kHist4Threads;
+        int    grid = (int)(want < (size_t)c->num_sms ? want : (size_t)c->num_sms);
+        if (grid < 1)
+            grid = 1;
+        sort_hist4_kernel<<<grid, kHist4Threads, 4 * kRadix * 32 * 4, stream>>>(d_srcKey, N, flip, ghist, hticket);
+        B200_TRY(cudaGetLastError());
+    }
 
     const uint32_t *kin = d_srcKey, *vin = d_srcVal;
     for (int p = 0; p < 4; p++) {
         uint32_t *kout = (p & 1) ? d_dstKey : d_bufKey;
         uint32_t *vout = (p & 1) ? d_dstVal : d_bufVal;
         unsigned *desc = reinterpret_cast<unsigned *>(base + kSortOffDesc + p * desc_bytes);
-        sort_pass_kernel<false><<<tiles, kSortThreads, sizeof(SortSmem), stream>>>(
-            kin, vin, kout, vout, (unsigned)N, 8u * p, flip, nullptr, 0, ghist + p * kRadix, tickets + p, desc);
-        B200_TRY(cudaGetLastError());
+        B200_TRY((cudaError_t)launch_pass_lb<false>(tiles, stream, kin, vin, kout, vout, (unsigned)N, 8u * p, flip,
+                                                    (const unsigned *)nullptr, 0u, (const unsigned *)(ghist + p * kRadix),
+                                                    tickets + p, desc));
         kin = kout;
         vin = vout;
     }
@@ -416,7 +556,6 @@ extern "C" int b200_partition_kv_async(uint32_t *d_dstKey, uint32_t *d_dstVal, c
         B200_TRY(cudaMemsetAsync(d_bucketCounts, 0, numBuckets * 4, stream));
         return 0;
     }
-    B200_TRY((cudaError_t)prepare_pass_kernel<true>());
     const unsigned tiles      = (unsigned)((N + kSortTile - 1) / kSortTile);
     const size_t   desc_bytes = (size_t)tiles * kRadix * 4;
     const size_t   need       = kSortOffDesc + desc_bytes;
@@ -438,9 +577,16 @@ extern "C" int b200_partition_kv_async(uint32_t *d_dstKey, uint32_t *d_dstVal, c
     sort_hist_kernel<true><<<grid, kSortThreads, 0, stream>>>(d_srcKey, N, flip, d_splitters, nspl, ghist, hticket,
                                                             d_bucketCounts);
     B200_TRY(cudaGetLastError());
-    sort_pass_kernel<true><<<tiles, kSortThreads, sizeof(SortSmem), stream>>>(
-        d_srcKey, d_srcVal, d_dstKey, d_dstVal, (unsigned)N, 0u, flip, d_splitters, nspl, ghist, tickets, desc);
-    B200_TRY(cudaGetLastError());
+    B200_TRY((cudaError_t)launch_pass_lb<true>(tiles, stream, (const unsigned *)d_srcKey, (const unsigned *)d_srcVal,
+                                               d_dstKey, d_dstVal, (unsigned)N, 0u, flip, (const unsigned *)d_splitters,
+                                               nspl, (const unsigned *)ghist, tickets, desc));
     count_launch(2);
+    return 0;
+}
+
+// tuning knob for experiments (not part of the stable ABI)
+extern "C" int b200_tune_sort_lookback(int per_round)
+{
+    g_sort_lb = per_round;
     return 0;
 }

@@ -46,47 +46,57 @@ __device__ __forceinline__ unsigned long long make_desc(unsigned epoch, unsigned
 }
 
 // Warp 0: sum of the aggregates of the tiles before `tile` back to the nearest published prefix.
+// One poll inspects kLookWindow * 32 descriptors (all loads issued together, so a poll costs one L2
+// round trip): the front of published prefixes can only advance by one window per round trip, and a
+// 32-wide window caps the whole scan near 32 tiles * 64 KiB / 0.8 us = 2.6 TB/s on this part.
+template <int kLookWindow>
 __device__ __forceinline__ unsigned look_back(const unsigned long long *desc, unsigned tile, unsigned first_tile,
                                               unsigned epoch)
 {
     const unsigned lane   = lane_id();
     const unsigned want_a = (epoch << 2) | kStA, want_p = (epoch << 2) | kStP;
     unsigned       prefix = 0;
-    long long      base   = (long long)tile - 1;
+    long long      base   = (long long)tile - 1; // lane l of group j inspects tile base - 32 j - l
     while (true) {
-        const long long idx   = base - lane;
-        const bool      valid = idx >= (long long)first_tile;
-        unsigned        st = want_p, val = 0, pmask, firstp = 0;
-        bool            ok;
-        do {
-            if (valid) {
+        unsigned st[kLookWindow], val[kLookWindow];
+#pragma unroll
+        for (int j = 0; j < kLookWindow; j++) {
+            const long long idx = base - 32 * j - lane;
+            st[j]               = want_p; // before the array's first tile: a prefix of 0
+            val[j]              = 0;
+            if (idx >= (long long)first_tile) {
                 unsigned long long d = ld_relaxed_u64(desc + idx);
-                st                   = (unsigned)(d >> 32);
-                val                  = (unsigned)d;
+                st[j]                = (unsigned)(d >> 32);
+                val[j]               = (unsigned)d;
             }
-            pmask          = __ballot_sync(0xffffffffu, st == want_p);
-            unsigned rmask = __ballot_sync(0xffffffffu, st == want_p || st == want_a);
-            if (pmask) {
-                firstp        = __ffs(pmask) - 1;
-                unsigned need = (1u << firstp) - 1u;
-                ok            = (rmask & need) == need;
-            }
-            else
-                ok = (rmask == 0xffffffffu);
-        } while (!ok);
-        if (pmask) {
-            prefix += __reduce_add_sync(0xffffffffu, lane <= firstp ? val : 0u);
-            break;
         }
-        prefix += __reduce_add_sync(0xffffffffu, val);
-        base -= 32;
+        bool done = false;
+#pragma unroll
+        for (int j = 0; j < kLookWindow; j++) {
+            const unsigned pmask = __ballot_sync(0xffffffffu, st[j] == want_p);
+            const unsigned rmask = __ballot_sync(0xffffffffu, st[j] == want_p || st[j] == want_a);
+            if (pmask) {
+                const unsigned firstp = __ffs(pmask) - 1;
+                const unsigned need   = (1u << firstp) - 1u;
+                if ((rmask & need) == need) {
+                    prefix += __reduce_add_sync(0xffffffffu, lane <= firstp ? val[j] : 0u);
+                    done = true;
+                }
+                break; // either finished, or an aggregate before the prefix is still missing: poll again
+            }
+            if (rmask != 0xffffffffu)
+                break; // someone in this group has not published yet: poll again from here
+            prefix += __reduce_add_sync(0xffffffffu, val[j]);
+            base -= 32;
+        }
+        if (done)
+            return prefix;
     }
-    return prefix;
 }
 
 // kLarge: arrays of at least one tile (lane_seg=32, rows_seg=4, warps_seg=16 known at compile time)
 template <bool kLarge>
-__global__ void __launch_bounds__(kScanThreads)
+__global__ void __launch_bounds__(kScanThreads, 3)
     scan_kernel(unsigned *dst, const unsigned *src, const ScanParams p, // may alias (in place)
                 unsigned *__restrict__ state, unsigned long long *__restrict__ desc)
 {
@@ -99,14 +109,13 @@ __global__ void __launch_bounds__(kScanThreads)
     unsigned   tile = blockIdx.x, epoch = 0;
     if (chained) {
         if (threadIdx.x == 0) {
-            // epoch first (acquire), then the ticket: whoever holds a ticket has already read the
-            // epoch, so the CTA that draws the last ticket may advance it for the next launch.
-            unsigned ep = ld_acquire_u32(&state[1]);
-            unsigned t  = atomicAdd(&state[0], 1u);
-            if (t == p.num_tiles - 1) {
-                st_relaxed_u32(&state[0], 0u);
-                st_relaxed_u32(&state[1], (ep + 1u) & 0x3fffffffu);
-            }
+            // one 64-bit atomic returns {epoch (high) | ticket (low)}; every CTA draws exactly once, so
+            // the CTA that draws the last ticket can re-arm {epoch+1, 0} for the next launch.
+            const unsigned long long drawn = atomicAdd(reinterpret_cast<unsigned long long *>(state), 1ull);
+            const unsigned           t = (unsigned)drawn, ep = (unsigned)(drawn >> 32);
+            if (t == p.num_tiles - 1)
+                *reinterpret_cast<volatile unsigned long long *>(state) =
+                    (unsigned long long)((ep + 1u) & 0x3fffffffu) << 32;
             s_tile  = t;
             s_epoch = ep;
         }
@@ -226,7 +235,7 @@ __global__ void __launch_bounds__(kScanThreads)
             else {
                 if (lane == 0)
                     st_relaxed_u64(desc + tile, make_desc(epoch, kStA, aggregate));
-                prefix = look_back(desc, tile, first_tile, epoch); // the first tile's prefix already holds the carry
+                prefix = look_back<4>(desc, tile, first_tile, epoch); // the first tile's prefix already holds the carry
                 if (lane == 0)
                     st_relaxed_u64(desc + tile, make_desc(epoch, kStP, prefix + aggregate));
             }
@@ -263,7 +272,250 @@ __global__ void __launch_bounds__(kScanThreads)
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------------
+// Chained scan, persistent + TMA-staged (the hot case: arrays spanning several tiles, 16-byte aligned).
+// One CTA per SM, kTmaStages tiles of 32 KiB in flight in shared memory, four warp roles that only
+// meet through mbarriers (no CTA-wide barrier anywhere in the steady state):
+//   producer  (1 lane)   draws {epoch|ticket} with ONE 64-bit atomicAdd, streams the tile in with
+//                        cp.async.bulk (1-D TMA, SASS UBLKCP) and, once the scan warps have overwritten
+//                        the stage with results, streams it out with cp.async.bulk.global.shared;
+//   scan warps (16)      phase A on tile k+kAhead: per-warp total -> shared; the warp that completes the
+//                        tile's total publishes the look-back aggregate at once, long before the tile is
+//                        scanned.  Phase B on tile k: warp-striped scan in shared memory, seeded with the
+//                        tile prefix, conflict-free 16-byte shared accesses;
+//   look-back warps (2)  alternate over the CTA's tiles: wait for the tile's total, walk the descriptors
+//                        back (128 per poll), publish the inclusive prefix, hand the exclusive prefix to
+//                        the scan warps.  Look-back latency is off the scan warps' critical path.
+// Every CTA draws exactly one out-of-range ticket, so the draw numbered tiles+grid-1 is the last one and
+// its owner re-arms {epoch+1, ticket 0} for the next launch.
+// ---------------------------------------------------------------------------------------------------
+constexpr int      kTmaStages    = 6;
+constexpr int      kTmaAhead     = 3;                   // phase A runs this many tiles ahead of phase B
+constexpr int      kTmaLookWarps = 2;
+constexpr int      kTmaThreads   = kScanThreads + 32 * (1 + kTmaLookWarps); // 16 scan + 1 producer + 2 look-back
+constexpr unsigned kTileEnd      = 0xffffffffu;
+
+struct ScanTmaSmem {
+    unsigned buf[kTmaStages][kScanTile];    // 6 x 32 KiB
+    uint64_t full[kTmaStages];              // producer  -> all     : tile landed (tx bytes) / END marker
+    uint64_t agg_ready[kTmaStages];         // scan warps -> look-back: the 16 warp totals are in
+    uint64_t prefix_ready[kTmaStages];      // look-back -> scan warps: exclusive tile prefix is in
+    uint64_t scanned[kTmaStages];           // scan warps -> producer : results are in the stage
+    unsigned tile[kTmaStages], count[kTmaStages], epoch[kTmaStages];
+    unsigned wtot[kTmaStages][kScanWarps];  // per-warp totals of the tile
+    unsigned agg[kTmaStages], agg_cnt[kTmaStages];
+    unsigned prefix[kTmaStages];
+    unsigned end_index;                     // CTA-local index of the END marker (look-back warps)
+};
+
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+template <int kLookWindow>
+__global__ void __launch_bounds__(kTmaThreads, 1)
+    scan_tma_kernel(unsigned *dst, const unsigned *src, const ScanParams p, unsigned long long *state,
+                    unsigned long long *desc)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    ScanTmaSmem   &S    = *reinterpret_cast<ScanTmaSmem *>(smem_raw);
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kTmaStages; s++) {
+            mbar_init(&S.full[s], 1);
+            mbar_init(&S.agg_ready[s], kScanWarps);
+            mbar_init(&S.prefix_ready[s], 1);
+            mbar_init(&S.scanned[s], kScanWarps);
+            S.agg[s]     = 0;
+            S.agg_cnt[s] = 0;
+        }
+        S.end_index = 0xffffffffu;
+        fence_mbar_init();
+    }
+    __syncthreads();
+    const unsigned carry = p.carry ? __ldg(p.carry) : 0u;
+
+    if (warp == kScanWarps) {
+        // ================================ producer (one lane) ==========================================
+        if (lane != 0)
+            return;
+        unsigned k = 0;
+        while (true) {
+            const unsigned           s      = k % kTmaStages;
+            const unsigned long long drawn  = atomicAdd(state, 1ull);
+            const unsigned           ticket = (unsigned)drawn, epoch = (unsigned)(drawn >> 32);
+            if (k >= (unsigned)kTmaStages) {
+                // the tile that used this stage: wait for its results, stream them out, recycle the stage
+                mbar_wait(&S.scanned[s], (k / kTmaStages - 1) & 1);
+                const unsigned ot = S.tile[s], oa = ot / p.tpa;
+                bulk_s2g(dst + (size_t)oa * p.L + (size_t)(ot - oa * p.tpa) * kScanTile, S.buf[s], S.count[s] * 4u);
+                bulk_commit();
+                bulk_wait_read<0>();
+            }
+            if (ticket >= p.num_tiles) {
+                if (ticket == p.num_tiles + gridDim.x - 1) // the very last draw of this launch
+                    *reinterpret_cast<volatile unsigned long long *>(state) =
+                        (unsigned long long)((epoch + 1u) & 0x3fffffffu) << 32;
+                S.end_index = k;
+                S.tile[s]   = kTileEnd;
+                mbar_arrive(&S.full[s]);
+                // the look-back warps that own indices k+1 .. wait on the NEXT stages: wake them too
+                // (after the tile still landing in that stage, if any, has completed its phase)
+                for (unsigned j = 1; j < (unsigned)kTmaLookWarps; j++) {
+                    const unsigned kk = k + j, ss = kk % kTmaStages;
+                    if (kk >= (unsigned)kTmaStages)
+                        mbar_wait(&S.full[ss], (kk / kTmaStages - 1) & 1);
+                    mbar_arrive(&S.full[ss]);
+                }
+                break;
+            }
+            const unsigned a = ticket / p.tpa, t = ticket - a * p.tpa;
+            const size_t   off    = (size_t)a * p.L + (size_t)t * kScanTile;
+            const size_t   remain = p.L - (size_t)t * kScanTile;
+            const unsigned count  = remain < kScanTile ? (unsigned)remain : kScanTile;
+            S.tile[s]  = ticket;
+            S.count[s] = count;
+            S.epoch[s] = epoch;
+            mbar_expect_tx(&S.full[s], count * 4u);
+            bulk_g2s(S.buf[s], src + off, count * 4u, &S.full[s]);
+            k++;
+        }
+        // drain: tiles k-stages+1 .. k-1 (tile k-stages, if any, was streamed out just above)
+        const unsigned first = k >= (unsigned)kTmaStages ? k - kTmaStages + 1 : 0u;
+        for (unsigned j = first; j < k; j++) {
+            const unsigned s = j % kTmaStages;
+            mbar_wait(&S.scanned[s], (j / kTmaStages) & 1);
+            const unsigned ot = S.tile[s], oa = ot / p.tpa;
+            bulk_s2g(dst + (size_t)oa * p.L + (size_t)(ot - oa * p.tpa) * kScanTile, S.buf[s], S.count[s] * 4u);
+            bulk_commit();
+        }
+        bulk_wait_all<0>();
+        return;
+    }
+
+    if (warp > kScanWarps) {
+        // ================================ look-back warps ==============================================
+        for (unsigned k = warp - kScanWarps - 1;; k += kTmaLookWarps) {
+            const unsigned s = k % kTmaStages, par = (k / kTmaStages) & 1;
+            mbar_wait(&S.full[s], par);
+            if (k >= *reinterpret_cast<volatile unsigned *>(&S.end_index))
+                break;
+            const unsigned tile  = S.tile[s];
+            const unsigned epoch = S.epoch[s], first_tile = (tile / p.tpa) * p.tpa;
+            mbar_wait(&S.agg_ready[s], par);
+            const unsigned aggregate = S.agg[s];
+            unsigned       prefix    = carry;
+            if (tile != first_tile) { // (a first tile's inclusive prefix was published by the scan warps)
+                prefix = look_back<kLookWindow>(desc, tile, first_tile, epoch);
+                if (lane == 0)
+                    st_relaxed_u64(desc + tile, make_desc(epoch, kStP, prefix + aggregate));
+            }
+            __syncwarp();
+            if (lane == 0) {
+                S.prefix[s]  = prefix;
+                S.agg[s]     = 0;
+                S.agg_cnt[s] = 0;
+                mbar_arrive(&S.prefix_ready[s]);
+            }
+        }
+        return;
+    }
+
+    // ==================================== scan warps (16) ==============================================
+    unsigned a = 0, end_index = 0xffffffffu;
+    for (unsigned b = 0;; b++) {
+        // ---- phase A: warp totals of tiles up to kTmaAhead ahead; the completing warp publishes -------
+        while (end_index == 0xffffffffu && a <= b + kTmaAhead) {
+            const unsigned s = a % kTmaStages;
+            mbar_wait(&S.full[s], (a / kTmaStages) & 1);
+            const unsigned tile = S.tile[s];
+            if (tile == kTileEnd) {
+                end_index = a;
+                break;
+            }
+            const unsigned count = S.count[s];
+            unsigned       sum   = 0;
+#pragma unroll
+            for (int r = 0; r < kScanRows; r++) {
+                const unsigned e = warp * (kScanRows * 128) + r * 128 + lane * 4;
+                uint4          v = *reinterpret_cast<const uint4 *>(&S.buf[s][e]);
+                if (e < count) // ragged last tile of an array (count is a multiple of 4 here)
+                    sum += (v.x + v.y) + (v.z + v.w);
+            }
+            sum = __reduce_add_sync(0xffffffffu, sum);
+            if (lane == 0) {
+                S.wtot[s][warp] = sum;
+                atomicAdd(&S.agg[s], sum);
+                __threadfence_block();
+                if (atomicAdd(&S.agg_cnt[s], 1u) == kScanWarps - 1) {
+                    // all 16 warp totals are in: publish for the tiles behind us right away
+                    __threadfence_block();
+                    const unsigned agg        = *reinterpret_cast<volatile unsigned *>(&S.agg[s]);
+                    const unsigned first_tile = (tile / p.tpa) * p.tpa;
+                    st_relaxed_u64(desc + tile, tile == first_tile ? make_desc(S.epoch[s], kStP, carry + agg)
+                                                                   : make_desc(S.epoch[s], kStA, agg));
+                }
+                mbar_arrive(&S.agg_ready[s]);
+            }
+            a++;
+        }
+        if (b == end_index)
+            break;
+        // ---- phase B: scan tile b in place in shared memory --------------------------------------------
+        const unsigned s = b % kTmaStages;
+        mbar_wait(&S.prefix_ready[s], (b / kTmaStages) & 1);
+        const unsigned count = S.count[s];
+        uint4          v[kScanRows];
+        unsigned       ebase[kScanRows], tot[kScanRows], inc[kScanRows];
+#pragma unroll
+        for (int r = 0; r < kScanRows; r++) {
+            ebase[r] = warp * (kScanRows * 128) + r * 128 + lane * 4;
+            v[r]     = *reinterpret_cast<const uint4 *>(&S.buf[s][ebase[r]]);
+            if (ebase[r] >= count)
+                v[r] = make_uint4(0, 0, 0, 0);
+            tot[r] = (v[r].x + v[r].y) + (v[r].z + v[r].w);
+            inc[r] = tot[r];
+        }
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1)
+#pragma unroll
+            for (int r = 0; r < kScanRows; r++) {
+                unsigned t = __shfl_up_sync(0xffffffffu, inc[r], d);
+                if (lane >= d)
+                    inc[r] += t;
+            }
+        unsigned x = (lane < kScanWarps) ? S.wtot[s][lane] : 0u, xi = x;
+#pragma unroll
+        for (int d = 1; d < kScanWarps; d <<= 1) {
+            unsigned t = __shfl_up_sync(0xffffffffu, xi, d);
+            if (lane >= d)
+                xi += t;
+        }
+        unsigned run = S.prefix[s] + __shfl_sync(0xffffffffu, xi - x, warp);
+#pragma unroll
+        for (int r = 0; r < kScanRows; r++) {
+            const unsigned e0 = run + (inc[r] - tot[r]);
+            run += __shfl_sync(0xffffffffu, inc[r], 31);
+            uint4 o;
+            o.x = e0;
+            o.y = e0 + v[r].x;
+            o.z = o.y + v[r].y;
+            o.w = o.z + v[r].z;
+            *reinterpret_cast<uint4 *>(&S.buf[s][ebase[r]]) = o;
+        }
+        fence_proxy_async_smem(); // generic-proxy writes -> visible to the bulk-copy engine
+        __syncwarp();
+        if (lane == 0)
+            mbar_arrive(&S.scanned[s]);
+    }
+}
+
 static bool is_pow2(size_t x) { return x && !(x & (x - 1)); }
+static bool g_scan_use_tma = true;
+static int  g_scan_window  = 8; // look-back window in units of 32 descriptors
 
 } // namespace b200
 
@@ -315,12 +567,49 @@ extern "C" int b200_scan_exclusive_async(uint32_t *d_dst, const uint32_t *d_src,
     B200_TRY((cudaError_t)ensure(c->scan, 16 + 8 * ndesc, stream));
     unsigned           *state = reinterpret_cast<unsigned *>(c->scan.ptr);
     unsigned long long *desc  = reinterpret_cast<unsigned long long *>(reinterpret_cast<char *>(c->scan.ptr) + 16);
-    if (large)
+    const bool tma_ok = large && p.tpa > 1 && (L % 4) == 0 && g_scan_use_tma &&
+                        ((((uintptr_t)d_dst) | ((uintptr_t)d_src)) & 15) == 0;
+    if (tma_ok) {
+        unsigned grid = (unsigned)c->num_sms; // one persistent CTA per SM
+        if (grid > p.num_tiles)
+            grid = p.num_tiles;
+        auto *st64 = reinterpret_cast<unsigned long long *>(state);
+#define B200_LAUNCH_SCAN_TMA(W)                                                                                 \
+    do {                                                                                                        \
+        static bool prepared = false;                                                                           \
+        if (!prepared) {                                                                                        \
+            B200_TRY(cudaFuncSetAttribute(scan_tma_kernel<W>, cudaFuncAttributeMaxDynamicSharedMemorySize,      \
+                                          (int)sizeof(ScanTmaSmem)));                                           \
+            prepared = true;                                                                                    \
+        }                                                                                                       \
+        scan_tma_kernel<W><<<grid, kTmaThreads, sizeof(ScanTmaSmem), stream>>>(d_dst, d_src, p, st64, desc);    \
+    } while (0)
+        if (g_scan_window <= 4)
+            B200_LAUNCH_SCAN_TMA(4);
+        else if (g_scan_window <= 8)
+            B200_LAUNCH_SCAN_TMA(8);
+        else
+            B200_LAUNCH_SCAN_TMA(16);
+#undef B200_LAUNCH_SCAN_TMA
+    }
+    else if (large)
         scan_kernel<true><<<p.num_tiles, kScanThreads, 0, stream>>>(d_dst, d_src, p, state, desc);
     else
         scan_kernel<false><<<p.num_tiles, kScanThreads, 0, stream>>>(d_dst, d_src, p, state, desc);
     count_launch();
     B200_TRY(cudaGetLastError());
+    return 0;
+}
+
+// tuning knob for tests / bench (not part of the stable ABI): 0 = register-staged chained scan only
+extern "C" int b200_tune_scan_tma(int enable)
+{
+    g_scan_use_tma = enable != 0;
+    return 0;
+}
+extern "C" int b200_tune_scan_window(int groups)
+{
+    g_scan_window = groups;
     return 0;
 }
 

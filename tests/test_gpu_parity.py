@@ -331,6 +331,29 @@ def test_scan_full_size(prim):
     assert (dst.cpu().numpy().view(np.uint32) == oracle.scan_exclusive(src, 1024, 262144)).all()
 
 
+def test_scan_register_staged_path(prim):
+    """The chained scan has two stagings (TMA bulk copies by default, plain 16-byte loads otherwise):
+    both must give the gold result."""
+    from cuda_samples_b200._lib import lib
+    rng = np.random.default_rng(21)
+    try:
+        for enable in (0, 1):
+            lib.b200_tune_scan_tma(enable)
+            for batch, L in ((1, 1 << 22), (3, 8192 * 5 + 4), (2, 3 * 8192), (5, 1 << 16), (1, 8192 * 700 + 12)):
+                src = rng.integers(0, 2**32, batch * L, dtype=np.uint32)
+                got = run_scan(prim, dev(as_i32(src)), batch, L, short=False)
+                assert (got == oracle.scan_exclusive(src, batch, L)).all(), (enable, batch, L)
+            # many launches back to back: descriptors of earlier launches must never be taken for current ones
+            n = 1 << 20
+            src = rng.integers(0, 2**32, n, dtype=np.uint32)
+            d, dst = dev(as_i32(src)), torch.empty(n, dtype=torch.int32).cuda()
+            for _ in range(50):
+                prim.scanExclusiveLarge(dst, d, 1, n)
+            assert (dst.cpu().numpy().view(np.uint32) == oracle.scan_exclusive(src, 1, n)).all()
+    finally:
+        lib.b200_tune_scan_tma(1)
+
+
 def test_scan_dropin_symbols(prim):
     from cuda_samples_b200._lib import lib
     rng = np.random.default_rng(12)
