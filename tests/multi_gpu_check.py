@@ -1,0 +1,85 @@
+#!/usr/bin/env python3
+"""Parity of the sharded paths on real GPUs (one process per GPU, NCCL).  Launch with
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        tests/multi_gpu_check.py
+Every rank regenerates the global input with the counter-based generator on the CPU (oracle) and checks
+its own slice of the result against the oracle run on the whole input."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import cuda_samples_b200 as prim  # noqa: E402
+import oracle  # noqa: E402
+from cuda_samples_b200 import multi_gpu as mg  # noqa: E402
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    failures = []
+
+    def check(name, ok):
+        if not ok:
+            failures.append(name)
+
+    # histogram: 16 MiB per rank
+    n = 16 << 20
+    d = torch.empty(n, dtype=torch.uint8, device="cuda")
+    prim.generate(d, "bytes", rank * n, n, 2009)
+    h256, h64 = mg.histogram_sharded(d, n)
+    whole = oracle.generate("bytes", 0, world * n, 2009)
+    check("hist256", (h256.cpu().numpy().view(np.uint32) == oracle.histogram256(whole)).all())
+    check("hist64", (h64.cpu().numpy().view(np.uint32) == oracle.histogram64(whole)).all())
+
+    # reduce: 2^24 per rank
+    n = 1 << 24
+    xi = torch.empty(n, dtype=torch.int32, device="cuda")
+    xf = torch.empty(n, dtype=torch.float32, device="cuda")
+    prim.generate(xi, "i32_byte", rank * n, n, 1)
+    prim.generate(xf, "f32_byte", rank * n, n, 1)
+    gi, gf = mg.reduce_sharded(xi, n), mg.reduce_sharded(xf, n)
+    check("reduce_int", int(gi.item()) == oracle.reduce(oracle.generate("i32_byte", 0, world * n, 1)))
+    want = oracle.reduce(oracle.generate("f32_byte", 0, world * n, 1))
+    check("reduce_float", abs(float(gf.item()) - want) <= 1e-5 * abs(want))
+
+    # scan: one array of world * 2^24 elements, contiguous shards
+    src = torch.empty(n, dtype=torch.int32, device="cuda")
+    prim.generate(src, "u31", rank * n, n, 2009)
+    dst = torch.empty_like(src)
+    mg.scan_sharded(dst, src, n)
+    want = oracle.scan_exclusive(oracle.generate("u31", 0, world * n, 2009), 1, world * n)[rank * n:(rank + 1) * n]
+    check("scan", (dst.cpu().numpy().view(np.uint32) == want).all())
+
+    # sort: world * 2^22 pairs, three datasets, both directions
+    n = 1 << 22
+    for kind, param in (("key_unique", 0), ("key_tile_unique", 1 << 12), ("key_mod", 1000)):
+        keys = oracle.generate(kind, 0, world * n, 7, param)
+        vals = np.arange(world * n, dtype=np.uint32)
+        for direction in (1, 0):
+            sk = torch.from_numpy(keys[rank * n:(rank + 1) * n].view(np.int32).copy()).cuda()
+            sv = torch.from_numpy(vals[rank * n:(rank + 1) * n].view(np.int32).copy()).cuda()
+            dk, dv, n_out, m = mg.sort_sharded(sk, sv, n, direction)
+            wk, wv = oracle.stable_sort_kv(keys, vals, direction)
+            off = int(m[:, :rank].sum())  # rows = source, cols = destination: everything sent to lower ranks
+            gk, gv = dk[:n_out].cpu().numpy().view(np.uint32), dv[:n_out].cpu().numpy().view(np.uint32)
+            check("sort %s dir=%d" % (kind, direction),
+                  int(m.sum()) == world * n and (gk == wk[off:off + n_out]).all() and (gv == wv[off:off + n_out]).all())
+
+    flag = torch.tensor([len(failures)], dtype=torch.int32, device="cuda")
+    dist.all_reduce(flag)
+    if failures:
+        print("rank %d FAILED: %s" % (rank, failures), flush=True)
+    if rank == 0:
+        print("multi_gpu_check world=%d: %s" % (world, "OK" if int(flag.item()) == 0 else "FAILED"), flush=True)
+    dist.destroy_process_group()
+    sys.exit(1 if int(flag.item()) else 0)
+
+
+if __name__ == "__main__":
+    main()
