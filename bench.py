@@ -173,7 +173,7 @@ def run_reference(args):
                                        "oracle/oracle.c) over 2^26 elements each per step, one contiguous chunk per "
                                        "thread, partials added"},
             "e2e": {"value": gbs, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ---------------------------------------------------------------------------------- primitives table
@@ -384,12 +384,30 @@ def run_ours(args):
                     "d2h_bytes_per_step": 8, "steps": e2e_steps,
                     "api": "b200_reduce_i32_host + b200_reduce_f32_host (pinned host input, chunked H2D overlap)"},
             "gpu_launches": int(launches), "parity": parity, "primitives": table}
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """Libraries (NCCL's version banner, torchrun notices) write to fd 1; the contract is ONE JSON line on
+    stdout, so everything else is sent to stderr and the line is written to the saved descriptor."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line):
+    sys.stdout.flush()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, (json.dumps(line) + "\n").encode())
+
+
 def main():
+    quiet_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
