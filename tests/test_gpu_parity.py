@@ -538,3 +538,24 @@ def test_host_variants(prim):
         prim.sort_kv_host(ok, ov, keys, vals, keys.size, direction)
         wk, wv = oracle.stable_sort_kv(keys, vals, direction)
         assert (ok == wk).all() and (ov == wv).all()
+
+
+# ============================================================== unmodified sample drivers (drop-in)
+@pytest.mark.parametrize("name,args", [("histogram", []), ("scan", []), ("mergeSort", []),
+                                       ("reduction", ["--type=int"]), ("reduction", ["--type=float"]),
+                                       ("reduction", ["--type=double"])])
+def test_unmodified_sample_driver_links_and_passes(prim, name, args):
+    """baseline/_ref/<sample>_b200 = the reference's own main.cpp + gold files, linked against
+    libb200prim.so instead of the sample's .cu (baseline/build.py).  The driver makes its own input,
+    calls the entry points, runs its own gold and exits 0 only when they agree."""
+    import os
+    import subprocess
+    exe = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "baseline", "_ref", name + "_b200")
+    if not os.path.exists(exe):
+        pytest.skip("baseline/_ref not built (needs /root/reference at build time)")
+    r = subprocess.run([exe] + args, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    if name == "reduction":
+        assert "Test passed" in r.stdout
+    if name == "mergeSort":
+        assert "stable!" in r.stdout
