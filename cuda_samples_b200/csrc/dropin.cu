@@ -55,9 +55,8 @@ extern const uint MAX_LARGE_ARRAY_SIZE = 262144;
 
 void initScan(void)
 {
-    int st = 0;
-    if (!b200::ctx(&st))
-        B200_OR_DIE(st, "initScan");
+    // the sample allocates its scratch here (scan.cu:184-187); pre-size ours for MAX_BATCH_ELEMENTS
+    B200_OR_DIE(b200_scan_reserve(64u * 1048576u), "initScan");
 }
 void closeScan(void) { B200_OR_DIE(b200_release_scratch(), "closeScan"); }
 
@@ -75,9 +74,8 @@ size_t scanExclusiveLarge(uint *d_Dst, uint *d_Src, uint batchSize, uint arrayLe
 // ---- mergeSort ----------------------------------------------------------------------------------------
 void initMergeSort(void)
 {
-    int st = 0;
-    if (!b200::ctx(&st))
-        B200_OR_DIE(st, "initMergeSort");
+    // the sample allocates its scratch here (mergeSort.cu:455-461); pre-size ours for its maximum N = 2^22
+    B200_OR_DIE(b200_sort_reserve(4u * 1048576u), "initMergeSort");
 }
 void closeMergeSort(void) { B200_OR_DIE(b200_release_scratch(), "closeMergeSort"); }
 

@@ -590,3 +590,19 @@ extern "C" int b200_tune_sort_lookback(int per_round)
     g_sort_lb = per_round;
     return 0;
 }
+
+// Pre-size the sort scratch for up to N pairs (what initMergeSort() does for the sample's N <= 2^22, so the
+// sample's single cold timed call does not pay for cudaMalloc: mergeSort.cu:455-461 allocates there too).
+extern "C" int b200_sort_reserve(size_t N)
+{
+    int        st = 0;
+    DeviceCtx *c  = ctx(&st);
+    if (!c)
+        return st;
+    const size_t tiles = (N + kSortTile - 1) / kSortTile;
+    B200_TRY((cudaError_t)ensure(c->sort, kSortOffDesc + 4 * tiles * kRadix * 4, 0));
+    B200_TRY(cudaFuncSetAttribute(sort_hist4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * kRadix * 32 * 4));
+    B200_TRY(cudaFuncSetAttribute(sort_pass_kernel<false, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)sizeof(SortSmem)));
+    return 0;
+}

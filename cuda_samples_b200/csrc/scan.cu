@@ -619,3 +619,14 @@ extern "C" int b200_scan_total_async(uint32_t *d_total, const uint32_t *d_src, s
     return b200_reduce_i32_async(reinterpret_cast<const int32_t *>(d_src), n, reinterpret_cast<int32_t *>(d_total), 1,
                                  stream);
 }
+
+// Pre-size the descriptor scratch for scans of up to n elements in one array (initScan()).
+extern "C" int b200_scan_reserve(size_t n)
+{
+    int        st = 0;
+    DeviceCtx *c  = ctx(&st);
+    if (!c)
+        return st;
+    B200_TRY((cudaError_t)ensure(c->scan, 16 + 8 * ((n + kScanTile - 1) / kScanTile), 0));
+    return 0;
+}
