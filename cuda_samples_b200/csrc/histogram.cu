@@ -99,8 +99,17 @@ __global__ void __launch_bounds__(kHistThreads, 1)
         for (int k = 0; k < kHistUnroll; k++)
             count_vec<BINS, SH>(table, lane4, r[k]);
     }
-    for (; v < nvec; v += stride)
-        count_vec<BINS, SH>(table, lane4, ld_stream_u4(vin + v));
+    if (v < nvec) { // last partial round: keep the loads independent (no one-at-a-time latency chain)
+        uint4 r[kHistUnroll - 1];
+#pragma unroll
+        for (int k = 0; k < kHistUnroll - 1; k++)
+            if (v + k * stride < nvec)
+                r[k] = ld_stream_u4(vin + v + k * stride);
+#pragma unroll
+        for (int k = 0; k < kHistUnroll - 1; k++)
+            if (v + k * stride < nvec)
+                count_vec<BINS, SH>(table, lane4, r[k]);
+    }
     if (blockIdx.x == 0) { // ragged head / tail bytes
         for (size_t i = threadIdx.x; i < head; i += kHistThreads)
             atomicAdd(&table[(unsigned)(data[i] >> SH) * 32 + lane], 1u);

@@ -24,9 +24,10 @@
 
 namespace b200 {
 
-constexpr int      kSortThreads = 512;
+constexpr int      kSortThreads = 256;
 constexpr int      kSortWarps   = kSortThreads / 32;
 constexpr int      kSortItems   = 16;
+constexpr int      kSortCtasPerSm = 4;
 constexpr unsigned kSortTile    = kSortThreads * kSortItems; // 8192 pairs
 constexpr int      kRadix       = 256;
 constexpr unsigned kDescA = 1u << 30, kDescP = 2u << 30, kDescValue = (1u << 30) - 1;
@@ -290,7 +291,7 @@ __global__ void __launch_bounds__(kHist4Threads, 1)
 // cheaper than MATCH.ANY.  Index order inside the tile = (warp, item, lane), so ranks are stable.
 // ---------------------------------------------------------------------------------------------------
 template <bool kBucket, int kLB>
-__global__ void __launch_bounds__(kSortThreads, 2)
+__global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
     sort_pass_kernel(const unsigned *__restrict__ kin, const unsigned *__restrict__ vin, unsigned *__restrict__ kout,
                      unsigned *__restrict__ vout, unsigned n, unsigned shift, unsigned flip,
                      const unsigned *__restrict__ splitters, unsigned nspl, const unsigned *__restrict__ gbase,

@@ -149,8 +149,15 @@ __global__ void __launch_bounds__(kReduceThreads, kReduceCtasPerSm)
             r[k] = ld_stream_u4(vin + v + k * stride);
         acc.add_vecs(r);
     }
-    for (; v < nvec; v += stride)
-        acc.add_vec(ld_stream_u4(vin + v));
+    if (v < nvec) { // last partial round: independent guarded loads (no one-at-a-time latency chain)
+        uint4 r[kReduceUnroll - 1];
+#pragma unroll
+        for (int k = 0; k < kReduceUnroll - 1; k++)
+            r[k] = (v + k * stride < nvec) ? ld_stream_u4(vin + v + k * stride) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+        for (int k = 0; k < kReduceUnroll - 1; k++)
+            acc.add_vec(r[k]); // zeros are exact no-ops for every T
+    }
     if (blockIdx.x == 0) {
         for (size_t i = threadIdx.x; i < head; i += kReduceThreads)
             acc.add_scalar(in[i]);
