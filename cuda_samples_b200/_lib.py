@@ -7,7 +7,7 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200prim.so")
+LIB_PATH = os.environ.get("B200PRIM_LIB") or os.path.join(_HERE, "libb200prim.so")  # override: debug builds only
 
 vp = ctypes.c_void_p
 sz = ctypes.c_size_t
@@ -45,6 +45,7 @@ SIGNATURES = {
     "b200_tune_hist_cluster": (ci, [ci]),
     "b200_tune_scan_tma": (ci, [ci]),
     "b200_tune_scan_window": (ci, [ci]),
+    "b200_tune_scan_backoff": (ci, [ci]),
     "b200_tune_sort_lookback": (ci, [ci]),
     # drop-in entry points (the samples' own signatures)
     "initHistogram64": (None, []), "closeHistogram64": (None, []), "histogram64": (None, [vp, vp, u32]),

@@ -38,7 +38,12 @@ def _compile(src, obj, verbose):
     return obj
 
 
-def build(force=False, verbose=False):
+def build(force=False, verbose=False, trace=False):
+    global OBJ, LIB, FLAGS
+    if trace:  # debug variant with per-tile pipeline timestamps (profiles/scan_trace.py)
+        OBJ = os.path.join(HERE, "build_trace")
+        LIB = os.path.join(HERE, "libb200prim_trace.so")
+        FLAGS = FLAGS + ["-DB200_SCAN_TRACE"]
     srcs = sorted(glob.glob(os.path.join(CSRC, "*.cu")))
     hdrs = glob.glob(os.path.join(CSRC, "*.cuh")) + glob.glob(os.path.join(CSRC, "*.h")) + \
         glob.glob(os.path.join(os.path.dirname(HERE), "include", "*.h"))
@@ -58,4 +63,4 @@ def build(force=False, verbose=False):
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv))
+    print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv, trace="--trace" in sys.argv))

@@ -175,6 +175,11 @@ __device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gsrc, unsig
                  "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
 }
+// global -> L2 only (no shared memory is reserved while the line is in flight)
+__device__ __forceinline__ void bulk_prefetch_l2(const void *gsrc, unsigned bytes)
+{
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gsrc), "r"(bytes) : "memory");
+}
 // shared -> global, tracked by the bulk async-group
 __device__ __forceinline__ void bulk_s2g(void *gdst, const void *smem_src, unsigned bytes)
 {

@@ -38,6 +38,7 @@ struct ScanParams {
     unsigned        warps_seg;  // warps per array inside a tile     (16 when L >= 8192)
     unsigned        packed;     // 1: power-of-two L < tile, tiles cover whole arrays back to back
     const unsigned *carry;      // nullable: seed of element 0 of every array
+    unsigned        backoff_ns; // pause between unsuccessful look-back polls
 };
 
 __device__ __forceinline__ unsigned long long make_desc(unsigned epoch, unsigned state, unsigned value)
@@ -45,19 +46,39 @@ __device__ __forceinline__ unsigned long long make_desc(unsigned epoch, unsigned
     return ((unsigned long long)((epoch << 2) | state) << 32) | value;
 }
 
+#ifdef B200_SCAN_TRACE
+// Debug build only (cuda_samples_b200/build.py --trace): per-tile timestamps of the pipeline events.
+__device__ unsigned long long *g_scan_trace = nullptr; // [num_tiles][8]
+__device__ __forceinline__ unsigned long long trace_now()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#define SCAN_TRACE(tile, slot) \
+    do { if (g_scan_trace) g_scan_trace[(size_t)(tile) * 8 + (slot)] = trace_now(); } while (0)
+#define SCAN_TRACE_VAL(tile, slot, v) \
+    do { if (g_scan_trace) g_scan_trace[(size_t)(tile) * 8 + (slot)] = (v); } while (0)
+#else
+#define SCAN_TRACE(tile, slot) do { } while (0)
+#define SCAN_TRACE_VAL(tile, slot, v) do { } while (0)
+#endif
+
 // Warp 0: sum of the aggregates of the tiles before `tile` back to the nearest published prefix.
 // One poll inspects kLookWindow * 32 descriptors (all loads issued together, so a poll costs one L2
 // round trip): the front of published prefixes can only advance by one window per round trip, and a
 // 32-wide window caps the whole scan near 32 tiles * 64 KiB / 0.8 us = 2.6 TB/s on this part.
 template <int kLookWindow>
 __device__ __forceinline__ unsigned look_back(const unsigned long long *desc, unsigned tile, unsigned first_tile,
-                                              unsigned epoch)
+                                              unsigned epoch, unsigned backoff_ns = 0)
 {
     const unsigned lane   = lane_id();
     const unsigned want_a = (epoch << 2) | kStA, want_p = (epoch << 2) | kStP;
     unsigned       prefix = 0;
     long long      base   = (long long)tile - 1; // lane l of group j inspects tile base - 32 j - l
+    unsigned       polls  = 0;
     while (true) {
+        polls++;
         unsigned st[kLookWindow], val[kLookWindow];
 #pragma unroll
         for (int j = 0; j < kLookWindow; j++) {
@@ -89,8 +110,13 @@ __device__ __forceinline__ unsigned look_back(const unsigned long long *desc, un
             prefix += __reduce_add_sync(0xffffffffu, val[j]);
             base -= 32;
         }
-        if (done)
+        if (done) {
+            if (lane == 0)
+                SCAN_TRACE_VAL(tile, 4, polls);
             return prefix;
+        }
+        if (backoff_ns)
+            __nanosleep(backoff_ns);
     }
 }
 
@@ -274,6 +300,48 @@ __global__ void __launch_bounds__(kScanThreads, 3)
 
 
 // ---------------------------------------------------------------------------------------------------
+// Two-level look-back (used by the TMA kernel).  Polling a flat descriptor array has two costs on this
+// part: the front of published prefixes advances by at most one window per L2 round trip, and a wide
+// window makes every in-flight tile hammer the same few L2 lines, which measurably slows ALL traffic
+// (profiles/r01_scan_trace*.log: 256-wide window -> tile loads take 8 us, 32-wide -> 5 us).
+// So tiles are grouped in chunks of 32: level 1 = the <= 31 earlier tiles of the own chunk (one 256-byte
+// line, shared by 32 tiles only), level 2 = one descriptor per chunk {chunk total | prefix through the
+// chunk}, published by the chunk's last tile.  A hop on level 2 covers 32 chunks = 1024 tiles.
+// ---------------------------------------------------------------------------------------------------
+// One 32-wide window ending at index `last` (lane l inspects last - l, indices < first count as a
+// published prefix of 0).  Returns true when the window is decided: *found_p tells whether a prefix was
+// reached, *sum is the total of the aggregates after it (+ the prefix).  Returns false: poll again.
+__device__ __forceinline__ bool window32(const unsigned long long *desc, long long last, long long first,
+                                         unsigned want_a, unsigned want_p, bool *found_p, unsigned *sum)
+{
+    const unsigned  lane = lane_id();
+    const long long idx  = last - lane;
+    unsigned        st = want_p, val = 0;
+    if (idx >= first) {
+        unsigned long long d = ld_relaxed_u64(desc + idx);
+        st                   = (unsigned)(d >> 32);
+        val                  = (unsigned)d;
+    }
+    const unsigned pmask = __ballot_sync(0xffffffffu, st == want_p);
+    const unsigned rmask = __ballot_sync(0xffffffffu, st == want_p || st == want_a);
+    // lanes below `first` only exist to terminate the walk: a real prefix always comes first
+    const unsigned firstp = __ffs(pmask) - 1; // pmask != 0 whenever the window reaches `first`
+    if (pmask) {
+        const unsigned need = (1u << firstp) - 1u;
+        if ((rmask & need) != need)
+            return false;
+        *sum     = __reduce_add_sync(0xffffffffu, lane <= firstp ? val : 0u);
+        *found_p = (last - firstp) >= first; // a lane below `first` is the virtual "0" prefix
+        return true;
+    }
+    if (rmask != 0xffffffffu)
+        return false;
+    *sum     = __reduce_add_sync(0xffffffffu, val);
+    *found_p = false;
+    return true;
+}
+
+// ---------------------------------------------------------------------------------------------------
 // Chained scan, persistent + TMA-staged (the hot case: arrays spanning several tiles, 16-byte aligned).
 // One CTA per SM, kTmaStages tiles of 32 KiB in flight in shared memory, four warp roles that only
 // meet through mbarriers (no CTA-wide barrier anywhere in the steady state):
@@ -314,7 +382,6 @@ __device__ __forceinline__ void mbar_arrive(uint64_t *bar)
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
-template <int kLookWindow>
 __global__ void __launch_bounds__(kTmaThreads, 1)
     scan_tma_kernel(unsigned *dst, const unsigned *src, const ScanParams p, unsigned long long *state,
                     unsigned long long *desc)
@@ -336,25 +403,25 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
         fence_mbar_init();
     }
     __syncthreads();
-    const unsigned carry = p.carry ? __ldg(p.carry) : 0u;
+    const unsigned            carry = p.carry ? __ldg(p.carry) : 0u;
+    unsigned long long *const cdesc = desc + p.num_tiles; // chunk-level descriptors follow the tile-level ones
 
     if (warp == kScanWarps) {
         // ================================ producer (one lane) ==========================================
         if (lane != 0)
             return;
+        // Only the LOADS go through the bulk-copy engine.  Measured on B200: one SM's engine moves about
+        // 37 GB/s of 1-D bulk traffic, so 32 KiB in + 32 KiB out per tile caps the whole scan near 5.5 TB/s
+        // (and an extra L2 prefetch per tile lowers it to 4.3 TB/s); the results therefore leave through
+        // ordinary 16-byte stores from the scan warps' registers, which also frees the stage as soon as the
+        // tile has been read.
         unsigned k = 0;
         while (true) {
             const unsigned           s      = k % kTmaStages;
             const unsigned long long drawn  = atomicAdd(state, 1ull);
             const unsigned           ticket = (unsigned)drawn, epoch = (unsigned)(drawn >> 32);
-            if (k >= (unsigned)kTmaStages) {
-                // the tile that used this stage: wait for its results, stream them out, recycle the stage
+            if (k >= (unsigned)kTmaStages) // the scan warps have pulled the stage's previous tile into registers
                 mbar_wait(&S.scanned[s], (k / kTmaStages - 1) & 1);
-                const unsigned ot = S.tile[s], oa = ot / p.tpa;
-                bulk_s2g(dst + (size_t)oa * p.L + (size_t)(ot - oa * p.tpa) * kScanTile, S.buf[s], S.count[s] * 4u);
-                bulk_commit();
-                bulk_wait_read<0>();
-            }
             if (ticket >= p.num_tiles) {
                 if (ticket == p.num_tiles + gridDim.x - 1) // the very last draw of this launch
                     *reinterpret_cast<volatile unsigned long long *>(state) =
@@ -379,20 +446,11 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
             S.tile[s]  = ticket;
             S.count[s] = count;
             S.epoch[s] = epoch;
+            SCAN_TRACE(ticket, 0);
             mbar_expect_tx(&S.full[s], count * 4u);
             bulk_g2s(S.buf[s], src + off, count * 4u, &S.full[s]);
             k++;
         }
-        // drain: tiles k-stages+1 .. k-1 (tile k-stages, if any, was streamed out just above)
-        const unsigned first = k >= (unsigned)kTmaStages ? k - kTmaStages + 1 : 0u;
-        for (unsigned j = first; j < k; j++) {
-            const unsigned s = j % kTmaStages;
-            mbar_wait(&S.scanned[s], (j / kTmaStages) & 1);
-            const unsigned ot = S.tile[s], oa = ot / p.tpa;
-            bulk_s2g(dst + (size_t)oa * p.L + (size_t)(ot - oa * p.tpa) * kScanTile, S.buf[s], S.count[s] * 4u);
-            bulk_commit();
-        }
-        bulk_wait_all<0>();
         return;
     }
 
@@ -405,16 +463,68 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
                 break;
             const unsigned tile  = S.tile[s];
             const unsigned epoch = S.epoch[s], first_tile = (tile / p.tpa) * p.tpa;
+            if (lane == 0)
+                SCAN_TRACE(tile, 1);
             mbar_wait(&S.agg_ready[s], par);
+            if (lane == 0)
+                SCAN_TRACE(tile, 2);
             const unsigned aggregate = S.agg[s];
             unsigned       prefix    = carry;
             if (tile != first_tile) { // (a first tile's inclusive prefix was published by the scan warps)
-                prefix = look_back<kLookWindow>(desc, tile, first_tile, epoch);
-                if (lane == 0)
+                const unsigned want_a = (epoch << 2) | kStA, want_p = (epoch << 2) | kStP;
+                const unsigned t_in   = tile - first_tile, chunk_in = t_in >> 5;
+                const unsigned cpa    = (p.tpa + 31u) >> 5; // chunks per array
+                const unsigned chunk  = (tile / p.tpa) * cpa + chunk_in;
+                const bool     closes = (t_in & 31u) == 31u || t_in == p.tpa - 1; // last tile of its chunk
+                unsigned       sum1 = 0, polls = 0;
+                bool           found = false;
+                // level 1: earlier tiles of the own chunk
+                while (!window32(desc, (long long)tile - 1, (long long)first_tile + (chunk_in << 5), want_a, want_p,
+                                 &found, &sum1)) {
+                    polls++;
+                    if (p.backoff_ns)
+                        __nanosleep(p.backoff_ns);
+                }
+                if (found) {
+                    prefix = sum1; // reached a tile that already knows its inclusive prefix (carry included)
+                }
+                else {
+                    if (closes && lane == 0) // the chunk total is known before the chunk's prefix is
+                        st_relaxed_u64(cdesc + chunk, make_desc(epoch, kStA, sum1 + aggregate));
+                    // level 2: earlier chunks of the same array (chunk 0 always publishes a prefix)
+                    long long      last   = (long long)chunk - 1;
+                    const long long firstc = (long long)(tile / p.tpa) * cpa;
+                    unsigned       sum2   = 0;
+                    while (true) {
+                        unsigned part = 0;
+                        bool     fp   = false;
+                        if (!window32(cdesc, last, firstc, want_a, want_p, &fp, &part)) {
+                            polls++;
+                            if (p.backoff_ns)
+                                __nanosleep(p.backoff_ns);
+                            continue;
+                        }
+                        sum2 += part;
+                        if (fp)
+                            break;
+                        if (last - 31 < firstc) { // walked past the array's first chunk (cannot happen: chunk 0
+                            sum2 += carry;        // always publishes a prefix) -- the seed is the carry
+                            break;
+                        }
+                        last -= 32;
+                    }
+                    prefix = sum2 + sum1;
+                }
+                if (lane == 0) {
+                    SCAN_TRACE_VAL(tile, 4, polls + 1);
                     st_relaxed_u64(desc + tile, make_desc(epoch, kStP, prefix + aggregate));
+                    if (closes)
+                        st_relaxed_u64(cdesc + chunk, make_desc(epoch, kStP, prefix + aggregate));
+                }
             }
             __syncwarp();
             if (lane == 0) {
+                SCAN_TRACE(tile, 3);
                 S.prefix[s]  = prefix;
                 S.agg[s]     = 0;
                 S.agg_cnt[s] = 0;
@@ -468,6 +578,8 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
         const unsigned s = b % kTmaStages;
         mbar_wait(&S.prefix_ready[s], (b / kTmaStages) & 1);
         const unsigned count = S.count[s];
+        if (threadIdx.x == 0)
+            SCAN_TRACE(S.tile[s], 5);
         uint4          v[kScanRows];
         unsigned       ebase[kScanRows], tot[kScanRows], inc[kScanRows];
 #pragma unroll
@@ -495,6 +607,15 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
                 xi += t;
         }
         unsigned run = S.prefix[s] + __shfl_sync(0xffffffffu, xi - x, warp);
+        const unsigned tile_b = S.tile[s];
+        // everything this warp needs from the stage is in registers now: hand the stage back to the producer
+        __syncwarp();
+        if (threadIdx.x == 0)
+            SCAN_TRACE(tile_b, 6);
+        if (lane == 0)
+            mbar_arrive(&S.scanned[s]);
+        const unsigned ab = tile_b / p.tpa;
+        unsigned      *out = dst + (size_t)ab * p.L + (size_t)(tile_b - ab * p.tpa) * kScanTile;
 #pragma unroll
         for (int r = 0; r < kScanRows; r++) {
             const unsigned e0 = run + (inc[r] - tot[r]);
@@ -504,18 +625,16 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
             o.y = e0 + v[r].x;
             o.z = o.y + v[r].y;
             o.w = o.z + v[r].z;
-            *reinterpret_cast<uint4 *>(&S.buf[s][ebase[r]]) = o;
+            if (ebase[r] < count)
+                st_stream_u4(out + ebase[r], o);
         }
-        fence_proxy_async_smem(); // generic-proxy writes -> visible to the bulk-copy engine
-        __syncwarp();
-        if (lane == 0)
-            mbar_arrive(&S.scanned[s]);
     }
 }
 
 static bool is_pow2(size_t x) { return x && !(x & (x - 1)); }
 static bool g_scan_use_tma = true;
-static int  g_scan_window  = 8; // look-back window in units of 32 descriptors
+static int  g_scan_backoff_ns = 100;
+static int  g_scan_window  = 1; // (register-staged kernel only; the TMA kernel uses the two-level look-back)
 
 } // namespace b200
 
@@ -535,6 +654,7 @@ extern "C" int b200_scan_exclusive_async(uint32_t *d_dst, const uint32_t *d_src,
     p.total = batch * L;
     p.L     = L;
     p.carry = d_carry;
+    p.backoff_ns = (unsigned)g_scan_backoff_ns;
     bool large;
     if (L >= kScanTile || !is_pow2(L) || L < 4) {
         // tile-aligned arrays (look-back inside an array when it spans several tiles)
@@ -563,7 +683,8 @@ extern "C" int b200_scan_exclusive_async(uint32_t *d_dst, const uint32_t *d_src,
         large       = false;
     }
     // scratch: [0] ticket, [1] epoch, 64-bit descriptors from byte 16
-    size_t ndesc = (large && p.tpa > 1) ? p.num_tiles : 0;
+    // descriptors: one per tile, then one per chunk of 32 tiles of each array
+    size_t ndesc = (large && p.tpa > 1) ? (size_t)p.num_tiles + batch * (((size_t)p.tpa + 31) / 32) : 0;
     B200_TRY((cudaError_t)ensure(c->scan, 16 + 8 * ndesc, stream));
     unsigned           *state = reinterpret_cast<unsigned *>(c->scan.ptr);
     unsigned long long *desc  = reinterpret_cast<unsigned long long *>(reinterpret_cast<char *>(c->scan.ptr) + 16);
@@ -574,23 +695,13 @@ extern "C" int b200_scan_exclusive_async(uint32_t *d_dst, const uint32_t *d_src,
         if (grid > p.num_tiles)
             grid = p.num_tiles;
         auto *st64 = reinterpret_cast<unsigned long long *>(state);
-#define B200_LAUNCH_SCAN_TMA(W)                                                                                 \
-    do {                                                                                                        \
-        static bool prepared = false;                                                                           \
-        if (!prepared) {                                                                                        \
-            B200_TRY(cudaFuncSetAttribute(scan_tma_kernel<W>, cudaFuncAttributeMaxDynamicSharedMemorySize,      \
-                                          (int)sizeof(ScanTmaSmem)));                                           \
-            prepared = true;                                                                                    \
-        }                                                                                                       \
-        scan_tma_kernel<W><<<grid, kTmaThreads, sizeof(ScanTmaSmem), stream>>>(d_dst, d_src, p, st64, desc);    \
-    } while (0)
-        if (g_scan_window <= 4)
-            B200_LAUNCH_SCAN_TMA(4);
-        else if (g_scan_window <= 8)
-            B200_LAUNCH_SCAN_TMA(8);
-        else
-            B200_LAUNCH_SCAN_TMA(16);
-#undef B200_LAUNCH_SCAN_TMA
+        static bool prepared = false;
+        if (!prepared) {
+            B200_TRY(cudaFuncSetAttribute(scan_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)sizeof(ScanTmaSmem)));
+            prepared = true;
+        }
+        scan_tma_kernel<<<grid, kTmaThreads, sizeof(ScanTmaSmem), stream>>>(d_dst, d_src, p, st64, desc);
     }
     else if (large)
         scan_kernel<true><<<p.num_tiles, kScanThreads, 0, stream>>>(d_dst, d_src, p, state, desc);
@@ -612,6 +723,11 @@ extern "C" int b200_tune_scan_window(int groups)
     g_scan_window = groups;
     return 0;
 }
+extern "C" int b200_tune_scan_backoff(int ns)
+{
+    g_scan_backoff_ns = ns;
+    return 0;
+}
 
 extern "C" int b200_scan_total_async(uint32_t *d_total, const uint32_t *d_src, size_t n, b200_stream_t stream)
 {
@@ -627,6 +743,16 @@ extern "C" int b200_scan_reserve(size_t n)
     DeviceCtx *c  = ctx(&st);
     if (!c)
         return st;
-    B200_TRY((cudaError_t)ensure(c->scan, 16 + 8 * ((n + kScanTile - 1) / kScanTile), 0));
+    const size_t tiles = (n + kScanTile - 1) / kScanTile;
+    B200_TRY((cudaError_t)ensure(c->scan, 16 + 8 * (tiles + tiles / 32 + 64), 0));
     return 0;
 }
+
+#ifdef B200_SCAN_TRACE
+extern "C" int b200_debug_set_scan_trace(void *d_trace)
+{
+    unsigned long long *p = reinterpret_cast<unsigned long long *>(d_trace);
+    B200_TRY(cudaMemcpyToSymbol(g_scan_trace, &p, sizeof(p)));
+    return 0;
+}
+#endif

@@ -31,13 +31,13 @@ if "scan" in what:
     src = torch.empty(N, dtype=torch.int32, device="cuda")
     dst = torch.empty(N, dtype=torch.int32, device="cuda")
     prim.generate(src, "u31", 0, N, 2009)
-    for tma, win in ((0, 4), (1, 4), (1, 8), (1, 16)):
+    for tma, back in ((0, 0), (1, 0), (1, 100), (1, 200), (1, 400), (1, 800)):
         lib.b200_tune_scan_tma(tma)
-        lib.b200_tune_scan_window(win)
+        lib.b200_tune_scan_backoff(back)
         us = timeit(lambda: prim.scanExclusiveLarge(dst, src, 1, N), 20)
-        print("scan 2^28  tma=%d window=%3d descriptors: %8.1f us  %7.1f GB/s" % (tma, win * 32, us, 8 * N / us / 1e3))
+        print("scan 2^28  tma=%d backoff=%4d ns: %8.1f us  %7.1f GB/s" % (tma, back, us, 8 * N / us / 1e3))
     lib.b200_tune_scan_tma(1)
-    lib.b200_tune_scan_window(8)
+    lib.b200_tune_scan_backoff(0)
     for batch, L in ((1024, 1 << 18), (1 << 14, 1 << 14), (4, 1 << 26)):
         us = timeit(lambda: prim.scanExclusiveLarge(dst, src, batch, L), 20)
         print("scan batch=%d L=%d: %8.1f us  %7.1f GB/s" % (batch, L, us, 8 * N / us / 1e3))
