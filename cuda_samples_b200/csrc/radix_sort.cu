@@ -32,6 +32,21 @@ constexpr unsigned kSortTile    = kSortThreads * kSortItems; // 8192 pairs
 constexpr int      kRadix       = 256;
 constexpr unsigned kDescA = 1u << 30, kDescP = 2u << 30, kDescValue = (1u << 30) - 1;
 
+#ifdef B200_SCAN_TRACE
+// Debug build only: per-tile timestamps of the pass kernel's phases (profiles/sort_trace.py)
+__device__ unsigned long long *g_sort_trace = nullptr; // [tiles][8]
+__device__ __forceinline__ unsigned long long sort_now()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#define SORT_TRACE(tile, slot) \
+    do { if (g_sort_trace && threadIdx.x == 0) g_sort_trace[(size_t)(tile) * 8 + (slot)] = sort_now(); } while (0)
+#else
+#define SORT_TRACE(tile, slot) do { } while (0)
+#endif
+
 // shared memory of the pass kernel (dynamic, > 48 KiB)
 struct SortSmem {
     unsigned buf[kSortTile];              // keys in digit order
@@ -310,6 +325,7 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
         S.splitters[tid] = splitters[tid];
     __syncthreads();
     const unsigned   tile  = S.tile;
+    SORT_TRACE(tile, 0);
     const unsigned   base  = tile * kSortTile;
     const unsigned   valid = (n - base < kSortTile) ? (n - base) : kSortTile;
     const bool       full  = valid == kSortTile;
@@ -333,6 +349,11 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
     // ---- rank inside the warp, in index order -----------------------------------------------------------
     unsigned rank[kSortItems];
     uint2   *mywc = S.wc[warp];
+#ifdef B200_SCAN_TRACE
+    if (key[kSortItems - 1] == 0x12345678u)
+        SORT_TRACE(tile, 7); // (forces the last key load to complete before slot 1 is stamped)
+    SORT_TRACE(tile, 1);
+#endif
 #pragma unroll
     for (int i = 0; i < kSortItems; i++) {
         uint2 *slot = mywc + op(key[i]);
@@ -347,6 +368,7 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
         __syncwarp();
     }
 
+    SORT_TRACE(tile, 2);
     // values: issue the loads now, they are consumed after the look-back
     unsigned val[kSortItems];
     if (full) {
@@ -383,6 +405,7 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
             S.wsum[warp] = inc;
         tile_start = inc - count;
     }
+    SORT_TRACE(tile, 3);
     __syncthreads();
     if (tid < kRadix) {
         unsigned woff = 0;
@@ -417,8 +440,10 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
             st_relaxed_u32(desc + (size_t)tile * kRadix + tid, kDescP | (excl + count));
         }
         S.gofs[tid] = __ldg(gbase + tid) + excl - tile_start;
+        SORT_TRACE(tile, 4);
     }
     __syncthreads();
+    SORT_TRACE(tile, 5);
 
     // ---- keys and values: to shared memory in digit order, then out as contiguous runs per digit ----------
 #pragma unroll
@@ -428,6 +453,7 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
         S.vbuf[slot]        = val[i];
     }
     __syncthreads();
+    SORT_TRACE(tile, 6);
     if (full) {
 #pragma unroll
         for (int k = 0; k < kSortItems; k++) {
@@ -607,3 +633,12 @@ extern "C" int b200_sort_reserve(size_t N)
                                   (int)sizeof(SortSmem)));
     return 0;
 }
+
+#ifdef B200_SCAN_TRACE
+extern "C" int b200_debug_set_sort_trace(void *d_trace)
+{
+    unsigned long long *p = reinterpret_cast<unsigned long long *>(d_trace);
+    B200_TRY(cudaMemcpyToSymbol(g_sort_trace, &p, sizeof(p)));
+    return 0;
+}
+#endif

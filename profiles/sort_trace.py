@@ -1,0 +1,49 @@
+#!/usr/bin/env python3
+"""Per-tile timeline of one radix pass (debug build: python cuda_samples_b200/build.py --trace).
+    B200PRIM_LIB=cuda_samples_b200/libb200prim_trace.so python profiles/sort_trace.py
+Slots (globaltimer ns, thread 0 of each tile): 0 ticket drawn, 1 keys in registers, 2 ranked, 3 counts published,
+4 look-back done (digit 0), 5 all digits resolved (barrier), 6 keys+values staged in shared memory."""
+import ctypes
+import os
+import sys
+
+import numpy as np
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import cuda_samples_b200 as prim  # noqa: E402
+from cuda_samples_b200._lib import lib  # noqa: E402
+
+N = 1 << 28
+tiles = (N + 4095) // 4096
+sk = torch.empty(N, dtype=torch.int32, device="cuda")
+sv = torch.arange(N, dtype=torch.int32, device="cuda")
+dk, dv, bk, bv = (torch.empty(N, dtype=torch.int32, device="cuda") for _ in range(4))
+prim.generate(sk, "key_unique", 0, N, 2009)
+for _ in range(2):
+    prim.mergeSort(dk, dv, bk, bv, sk, sv, N, 1)
+trace = torch.zeros(tiles * 8, dtype=torch.int64, device="cuda")
+lib.b200_debug_set_sort_trace.argtypes = [ctypes.c_void_p]
+lib.b200_debug_set_sort_trace(ctypes.c_void_p(trace.data_ptr()))
+torch.cuda.synchronize()
+prim.mergeSort(dk, dv, bk, bv, sk, sv, N, 1)  # the 4 passes overwrite each other: the trace shows the last pass
+torch.cuda.synchronize()
+lib.b200_debug_set_sort_trace(ctypes.c_void_p(0))
+t = trace.cpu().numpy().reshape(tiles, 8).astype(np.float64)
+mid = slice(tiles // 4, 3 * tiles // 4)
+
+
+def stat(name, x):
+    x = x[mid]
+    print("%-40s mean %7.2f us  p10 %7.2f  p50 %7.2f  p90 %7.2f" % (name, x.mean() / 1e3, np.percentile(x, 10) / 1e3,
+                                                                  np.percentile(x, 50) / 1e3, np.percentile(x, 90) / 1e3))
+
+
+print("pass span %.1f us for %d tiles" % ((t[:, 6].max() - t[:, 0].min()) / 1e3, tiles))
+stat("ticket -> keys in registers", t[:, 1] - t[:, 0])
+stat("ranking (16 items)", t[:, 2] - t[:, 1])
+stat("barrier + warp order + publish", t[:, 3] - t[:, 2])
+stat("look-back (digit 0)", t[:, 4] - t[:, 3])
+stat("wait for all digits (barrier)", t[:, 5] - t[:, 4])
+stat("scatter to shared memory", t[:, 6] - t[:, 5])
+stat("TOTAL ticket -> staged", t[:, 6] - t[:, 0])
