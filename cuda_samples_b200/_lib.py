@@ -28,6 +28,7 @@ SIGNATURES = {
     "b200_reduce_i32_async": (ci, [vp, sz, vp, sz, vp]),
     "b200_reduce_f32_async": (ci, [vp, sz, vp, sz, vp]),
     "b200_reduce_f64_async": (ci, [vp, sz, vp, sz, vp]),
+    "b200_reduce_partial_async": (ci, [ci, vp, sz, vp, vp]),
     "b200_scan_exclusive_async": (ci, [vp, vp, sz, sz, vp, vp]),
     "b200_scan_total_async": (ci, [vp, vp, sz, vp]),
     "b200_sort_kv_async": (ci, [vp, vp, vp, vp, vp, vp, sz, u32, vp]),

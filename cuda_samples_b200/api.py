@@ -125,6 +125,15 @@ def reduce(size, threads, blocks, whichKernel, d_idata, d_odata, stream=None):
     check(fn(_dptr(d_idata), size, _dptr(d_odata), max(int(blocks), 1), _stream(stream)), "reduce<%s>" % kind)
 
 
+def reduce_partial(d_idata, size, d_slot_f64, stream=None):
+    """Shard partial of a sharded reduction: sum(d_idata[0:size]) in its own type, stored as a double."""
+    kind = {"i32": 0, "f32": 1, "f64": 2}.get(_REDUCE.get(str(d_idata.dtype)))
+    if kind is None:
+        raise TypeError("reduce_partial: unsupported dtype %s" % d_idata.dtype)
+    check(lib.b200_reduce_partial_async(kind, _dptr(d_idata), size, _dptr(d_slot_f64), _stream(stream)),
+          "reduce_partial")
+
+
 # ----------------------------------------------------------------------------------------- scan
 def initScan():
     lib.initScan()

@@ -121,7 +121,8 @@ template <typename Part> __device__ __forceinline__ Part block_sum(Part v, Part 
 template <typename L>
 __global__ void __launch_bounds__(kReduceThreads, kReduceCtasPerSm)
     reduce_kernel(const typename L::Elem *__restrict__ in, size_t n, typename L::Elem *__restrict__ out,
-                  size_t out_len, unsigned *__restrict__ ticket, typename L::Part *__restrict__ partials)
+                  size_t out_len, unsigned *__restrict__ ticket, typename L::Part *__restrict__ partials,
+                  double *__restrict__ out_f64)
 {
     typedef typename L::Elem Elem;
     typedef typename L::Part Part;
@@ -185,6 +186,8 @@ __global__ void __launch_bounds__(kReduceThreads, kReduceCtasPerSm)
     if (threadIdx.x == 0) {
         if (out_len > 0)
             out[0] = (Elem)q;
+        if (out_f64) // shard partial for the multi-GPU combine: the typed result, widened exactly
+            out_f64[0] = (double)(Elem)q;
         *ticket = 0; // ready for the next call (stream-ordered)
     }
     for (size_t i = 1 + threadIdx.x; i < out_len; i += kReduceThreads)
@@ -193,7 +196,7 @@ __global__ void __launch_bounds__(kReduceThreads, kReduceCtasPerSm)
 
 template <typename L>
 static int launch_reduce(const typename L::Elem *d_in, size_t n, typename L::Elem *d_out, size_t out_len,
-                         cudaStream_t stream)
+                         cudaStream_t stream, double *d_out_f64 = nullptr)
 {
     int        st = 0;
     DeviceCtx *c  = ctx(&st);
@@ -209,7 +212,7 @@ static int launch_reduce(const typename L::Elem *d_in, size_t n, typename L::Ele
         grid = 1;
     unsigned *ticket   = reinterpret_cast<unsigned *>(c->reduce.ptr);
     auto     *partials = reinterpret_cast<typename L::Part *>(reinterpret_cast<char *>(c->reduce.ptr) + 16);
-    reduce_kernel<L><<<grid, kReduceThreads, 0, stream>>>(d_in, n, d_out, out_len, ticket, partials);
+    reduce_kernel<L><<<grid, kReduceThreads, 0, stream>>>(d_in, n, d_out, out_len, ticket, partials, d_out_f64);
     count_launch();
     B200_TRY(cudaGetLastError());
     return 0;
@@ -232,4 +235,16 @@ extern "C" int b200_reduce_f64_async(const double *d_in, size_t n, double *d_out
                                      b200_stream_t stream)
 {
     return launch_reduce<LaneF64>(d_in, n, d_out, out_len, (cudaStream_t)stream);
+}
+
+// Shard partial of a multi-GPU reduction: the sum of d_in[0..n) in its own type (wrapping for int), written as a
+// double to *d_slot so that partials of different types share one all_gather buffer.  kind: 0 i32, 1 f32, 2 f64.
+extern "C" int b200_reduce_partial_async(int kind, const void *d_in, size_t n, double *d_slot, b200_stream_t stream)
+{
+    switch (kind) {
+    case 0: return launch_reduce<LaneI32>((const int *)d_in, n, nullptr, 0, (cudaStream_t)stream, d_slot);
+    case 1: return launch_reduce<LaneF32>((const float *)d_in, n, nullptr, 0, (cudaStream_t)stream, d_slot);
+    case 2: return launch_reduce<LaneF64>((const double *)d_in, n, nullptr, 0, (cudaStream_t)stream, d_slot);
+    }
+    return (int)cudaErrorInvalidValue;
 }

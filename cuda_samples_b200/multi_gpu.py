@@ -39,6 +39,9 @@ class CudaOps:
         api.reduce(n, 256, 1, 7, x, out)
         return out
 
+    def reduce_partial(self, x, n, slot):
+        api.reduce_partial(x, n, slot)
+
     def scan_total(self, src, n):
         tot = torch.empty(1, dtype=torch.int32, device=src.device)
         api.scan_total(tot, src, n)
@@ -94,6 +97,56 @@ def reduce_sharded(x, n, ops=None, group=None):
     parts = torch.empty(world, dtype=part.dtype, device=part.device)
     dist.all_gather_into_tensor(parts, part, group=group)
     return parts.to(torch.float64).sum().to(part.dtype).reshape(1)  # fixed rank order
+
+
+class PendingReduce:
+    """Result of reduce_many_sharded: the collective may still be in flight (it runs on NCCL's own stream,
+    overlapping whatever the caller enqueues next); result() makes the current stream wait for it."""
+
+    def __init__(self, work, gathered, world, dtypes):
+        self.work, self.gathered, self.world, self.dtypes = work, gathered, world, dtypes
+
+    def result(self):
+        """-> float64 tensor [k]: entry i is the sum over ranks (rank order, fp64) of the i-th shard partial.
+        Integer entries are exact integers; apply the 32-bit wrap with typed()."""
+        if self.work is not None:
+            self.work.wait()
+            self.work = None
+        if self.world == 1:
+            return self.gathered
+        return self.gathered.view(self.world, -1).sum(0)
+
+    def typed(self):
+        """-> list of python scalars in the inputs' own types (int: wrapped to int32 like reduceCPU<int>)."""
+        vals = self.result().cpu().tolist()
+        out = []
+        for v, dt in zip(vals, self.dtypes):
+            if dt == torch.int32:
+                out.append(((int(v) + 2**31) % 2**32) - 2**31)
+            elif dt == torch.float32:
+                out.append(float(torch.tensor(v, dtype=torch.float64).to(torch.float32)))
+            else:
+                out.append(float(v))
+        return out
+
+
+def reduce_many_sharded(tensors, ns, ops=None, group=None, overlap=True):
+    """Several sharded reductions with ONE collective: every local kernel writes its shard partial (widened
+    exactly to a double) into one small buffer, the buffer is all_gathered once, and the per-rank partials are
+    added in rank order in fp64.  With overlap=True the all_gather is asynchronous (NCCL's stream), so it hides
+    behind the caller's next kernels.  -> PendingReduce"""
+    ops = ops or CudaOps()
+    rank, world = _world(group)
+    k = len(tensors)
+    buf = torch.empty(k, dtype=torch.float64, device=tensors[0].device)
+    for i, (x, n) in enumerate(zip(tensors, ns)):
+        ops.reduce_partial(x, n, buf[i:i + 1])
+    dtypes = [x.dtype for x in tensors]
+    if world == 1:
+        return PendingReduce(None, buf, 1, dtypes)
+    gathered = torch.empty(world * k, dtype=torch.float64, device=buf.device)
+    work = dist.all_gather_into_tensor(gathered, buf, group=group, async_op=overlap)
+    return PendingReduce(work if overlap else None, gathered, world, dtypes)
 
 
 # --------------------------------------------------------------------------------------------- scan

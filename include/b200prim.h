@@ -56,6 +56,9 @@ int b200_histogram_fused_async(uint32_t *d_hist256, uint32_t *d_hist64, const vo
 int b200_reduce_i32_async(const int32_t *d_in, size_t n, int32_t *d_out, size_t out_len, b200_stream_t stream);
 int b200_reduce_f32_async(const float *d_in, size_t n, float *d_out, size_t out_len, b200_stream_t stream);
 int b200_reduce_f64_async(const double *d_in, size_t n, double *d_out, size_t out_len, b200_stream_t stream);
+/* multi-GPU building block: the shard's sum in its own type (kind 0 i32 wrapping, 1 f32, 2 f64), widened exactly
+ * to a double in *d_slot, so partials of mixed types travel in ONE all_gather buffer. */
+int b200_reduce_partial_async(int kind, const void *d_in, size_t n, double *d_slot, b200_stream_t stream);
 
 /* scan: replaces scanExclusiveShort()/scanExclusiveLarge() (scan.cu:210-266): batchSize independent
  * exclusive +scans of arrayLength u32 each (wrap mod 2^32), single pass, 8 B of traffic per

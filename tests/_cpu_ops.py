@@ -25,6 +25,9 @@ class OracleOps:
         v = oracle.reduce(_np(x, n))
         return torch.tensor([v], dtype=x.dtype)
 
+    def reduce_partial(self, x, n, slot):
+        slot[0] = float(oracle.reduce(_np(x, n)))
+
     def scan_total(self, src, n):
         s = int(_np(src, n).view(np.uint32).astype(np.uint64).sum() % 2**32)
         return torch.from_numpy(np.array([s], np.uint32).view(np.int32).copy())

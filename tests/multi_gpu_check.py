@@ -47,6 +47,8 @@ def main():
     check("reduce_int", int(gi.item()) == oracle.reduce(oracle.generate("i32_byte", 0, world * n, 1)))
     want = oracle.reduce(oracle.generate("f32_byte", 0, world * n, 1))
     check("reduce_float", abs(float(gf.item()) - want) <= 1e-5 * abs(want))
+    ti, tf = mg.reduce_many_sharded([xi, xf], [n, n]).typed()
+    check("reduce_many", ti == int(gi.item()) and abs(tf - want) <= 1e-5 * abs(want))
 
     # scan: one array of world * 2^24 elements, contiguous shards
     src = torch.empty(n, dtype=torch.int32, device="cuda")

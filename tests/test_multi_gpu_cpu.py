@@ -49,6 +49,11 @@ def _worker(rank, world, port, case, q):
             gf = mg.reduce_sharded(torch.from_numpy(xf[rank * n:(rank + 1) * n].copy()), n, ops=ops)
             want = oracle.reduce(xf)
             ok = int(gi.item()) == oracle.reduce(xi) and abs(float(gf.item()) - want) <= 1e-5 * abs(want)
+            # the one-collective form (what bench.py times)
+            pend = mg.reduce_many_sharded([torch.from_numpy(xi[rank * n:(rank + 1) * n].copy()),
+                                           torch.from_numpy(xf[rank * n:(rank + 1) * n].copy())], [n, n], ops=ops)
+            ti, tf = pend.typed()
+            ok = ok and ti == oracle.reduce(xi) and abs(tf - want) <= 1e-5 * abs(want)
         elif case == "scan":
             n = (1 << 16) + 12
             src = rng.integers(0, 2**32, world * n, dtype=np.uint32)
