@@ -30,6 +30,7 @@ if ROOT not in sys.path:
 METRIC = "HBM GB/s (% of B200 peak) per primitive; sort Gkeys/s at 1/2/4/8 GPUs"
 N_ELEMS = 1 << 28
 WORKLOAD = "reduce<int> + reduce<float> SUM over 2^28 elements each per GPU (BASELINE configs[1])"
+OVERLAP = os.environ.get("B200_BENCH_OVERLAP", "0") == "1"  # async all_gather behind the next step's kernels
 HBM_NOMINAL = 8000.0
 HBM_FALLBACK = 6650.0  # /opt/skills/guides/B200_PROFILING.md, only when MEASURED_PEAKS.json is absent
 
@@ -299,7 +300,7 @@ def run_ours(args):
     def step():
         # both shard reductions, then ONE all_gather of the two partials; the collective of step i runs on NCCL's
         # stream while the kernels of step i+1 execute, and is consumed (summed in rank order) one step later
-        p = mg.reduce_many_sharded([xi, xf], [N_ELEMS, N_ELEMS])
+        p = mg.reduce_many_sharded([xi, xf], [N_ELEMS, N_ELEMS], overlap=OVERLAP)
         if res["pending"] is not None:
             res["pending"].result()
         res["last"] = res["pending"] or p

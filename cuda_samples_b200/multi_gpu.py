@@ -130,10 +130,10 @@ class PendingReduce:
         return out
 
 
-def reduce_many_sharded(tensors, ns, ops=None, group=None, overlap=True):
+def reduce_many_sharded(tensors, ns, ops=None, group=None, overlap=False):
     """Several sharded reductions with ONE collective: every local kernel writes its shard partial (widened
     exactly to a double) into one small buffer, the buffer is all_gathered once, and the per-rank partials are
-    added in rank order in fp64.  With overlap=True the all_gather is asynchronous (NCCL's stream), so it hides
+    added in rank order in fp64.  With overlap=True the all_gather is asynchronous (NCCL stream); measured on
     behind the caller's next kernels.  -> PendingReduce"""
     ops = ops or CudaOps()
     rank, world = _world(group)
