@@ -27,7 +27,7 @@ namespace cg = cooperative_groups;
 namespace b200 {
 
 constexpr int kHistThreads = 1024;
-constexpr int kHistUnroll  = 4;
+constexpr int kHistUnroll  = 8;
 
 enum HistMode { kHist256 = 0, kHist64 = 1, kHistFused = 2 };
 

@@ -72,3 +72,9 @@ if "hist" in what:
         us = timeit(step, 40, 8)
         print("hist256 64 MiB cluster=%d: %7.2f us  %7.1f GB/s" % (cl, us, n / us / 1e3))
     lib.b200_tune_hist_cluster(2)
+    del bufs
+    big = torch.empty(4 << 30, dtype=torch.uint8, device="cuda")
+    prim.generate(big, "bytes", 0, 4 << 30, 2009)
+    for nb in (256 << 20, 1 << 30, 4 << 30):
+        us = timeit(lambda: prim.histogram256(h, big, nb), 10, 3)
+        print("hist256 %5d MiB: %8.2f us  %7.1f GB/s" % (nb >> 20, us, nb / us / 1e3))
