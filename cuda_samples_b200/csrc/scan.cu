@@ -429,14 +429,7 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
                 S.end_index = k;
                 S.tile[s]   = kTileEnd;
                 mbar_arrive(&S.full[s]);
-                // the look-back warps that own indices k+1 .. wait on the NEXT stages: wake them too
-                // (after the tile still landing in that stage, if any, has completed its phase)
-                for (unsigned j = 1; j < (unsigned)kTmaLookWarps; j++) {
-                    const unsigned kk = k + j, ss = kk % kTmaStages;
-                    if (kk >= (unsigned)kTmaStages)
-                        mbar_wait(&S.full[ss], (kk / kTmaStages - 1) & 1);
-                    mbar_arrive(&S.full[ss]);
-                }
+                // (the scan warps pass the end on to the look-back warps through agg_ready)
                 break;
             }
             const unsigned a = ticket / p.tpa, t = ticket - a * p.tpa;
@@ -458,14 +451,11 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
         // ================================ look-back warps ==============================================
         for (unsigned k = warp - kScanWarps - 1;; k += kTmaLookWarps) {
             const unsigned s = k % kTmaStages, par = (k / kTmaStages) & 1;
-            mbar_wait(&S.full[s], par);
+            mbar_wait(&S.agg_ready[s], par); // all 16 warp totals are in -- or the scan warps reached the end
             if (k >= *reinterpret_cast<volatile unsigned *>(&S.end_index))
                 break;
             const unsigned tile  = S.tile[s];
             const unsigned epoch = S.epoch[s], first_tile = (tile / p.tpa) * p.tpa;
-            if (lane == 0)
-                SCAN_TRACE(tile, 1);
-            mbar_wait(&S.agg_ready[s], par);
             if (lane == 0)
                 SCAN_TRACE(tile, 2);
             const unsigned aggregate = S.agg[s];
@@ -544,6 +534,12 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
             const unsigned tile = S.tile[s];
             if (tile == kTileEnd) {
                 end_index = a;
+                // tell the look-back warps: the owners of indices a .. a+kTmaLookWarps-1 wait on agg_ready of those
+                // stages.  (Their previous phases completed and were consumed long ago: phase A is at most
+                // kTmaAhead tiles ahead of the prefixes the look-back warps have already delivered.)
+                if (lane == 0)
+                    for (unsigned jj = 0; jj < (unsigned)kTmaLookWarps; jj++)
+                        mbar_arrive(&S.agg_ready[(a + jj) % kTmaStages]);
                 break;
             }
             const unsigned count = S.count[s];
