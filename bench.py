@@ -248,6 +248,20 @@ def primitives_table(torch, dist, prim, mg, rank, world, peak, barrier):
             prim.scanExclusiveShort(dst, src, n // 1024, 1024)
         record("scanExclusiveShort_L1024_2^28", time_steps(torch, step_scan_short, 20, 4) / 20, 8 * N_ELEMS)
     del src, dst
+    # --- reduction sibling: batched dot products, 4096 vectors x 65536 floats (2 GiB read)
+    if world == 1:
+        vn, en = 4096, 65536
+        da = torch.empty(vn * en, dtype=torch.float32, device="cuda")
+        db = torch.empty(vn * en, dtype=torch.float32, device="cuda")
+        prim.generate(da, "f32_byte", 0, vn * en, 3)
+        prim.generate(db, "f32_byte", 1 << 40, vn * en, 3)
+        dc = torch.empty(vn, dtype=torch.float32, device="cuda")
+
+        def step_dot():
+            prim.scalarProd(dc, da, db, vn, en)
+        record("scalarProd_4096x65536", time_steps(torch, step_dot, 10, 3) / 10, 8 * vn * en,
+               {"note": "8 B per element pair"})
+        del da, db
     # --- key-value sort, 2^28 pairs in total (BASELINE configs[4]), dataset D1 (all keys distinct)
     sk = torch.empty(n, dtype=torch.int32, device="cuda")
     sv = torch.arange(rank * n, rank * n + n, dtype=torch.int64, device="cuda").to(torch.int32)

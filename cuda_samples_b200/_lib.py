@@ -29,6 +29,7 @@ SIGNATURES = {
     "b200_reduce_f32_async": (ci, [vp, sz, vp, sz, vp]),
     "b200_reduce_f64_async": (ci, [vp, sz, vp, sz, vp]),
     "b200_reduce_partial_async": (ci, [ci, vp, sz, vp, vp]),
+    "b200_scalar_prod_async": (ci, [vp, vp, vp, ci, ci, vp]),
     "b200_scan_exclusive_async": (ci, [vp, vp, sz, sz, vp, vp]),
     "b200_scan_total_async": (ci, [vp, vp, sz, vp]),
     "b200_sort_kv_async": (ci, [vp, vp, vp, vp, vp, vp, sz, u32, vp]),
@@ -55,6 +56,8 @@ SIGNATURES = {
     "scanExclusiveShort": (sz, [vp, vp, u32, u32]), "scanExclusiveLarge": (sz, [vp, vp, u32, u32]),
     "initMergeSort": (None, []), "closeMergeSort": (None, []),
     "mergeSort": (None, [vp, vp, vp, vp, vp, vp, u32, u32]),
+    "reduce": (None, [ci, ci, ci, vp, vp]), "reduceSinglePass": (None, [ci, ci, ci, vp, vp]),
+    "reduceSinglePassMultiBlockCG": (None, [ci, ci, ci, vp, vp]), "scalarProd": (None, [vp, vp, vp, ci, ci]),
     "_Z6reduceIiEviiiiPT_S1_": (None, [ci, ci, ci, ci, vp, vp]),
     "_Z6reduceIfEviiiiPT_S1_": (None, [ci, ci, ci, ci, vp, vp]),
     "_Z6reduceIdEviiiiPT_S1_": (None, [ci, ci, ci, ci, vp, vp]),

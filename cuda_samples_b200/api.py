@@ -134,6 +134,18 @@ def reduce_partial(d_idata, size, d_slot_f64, stream=None):
           "reduce_partial")
 
 
+def reduceSinglePass(size, threads, blocks, d_idata, d_odata, stream=None):
+    """threadFenceReduction / reductionMultiBlockCG entry point (float): d_odata[0] = sum, rest zero."""
+    check(lib.b200_reduce_f32_async(_dptr(d_idata), size, _dptr(d_odata), max(int(blocks), 1), _stream(stream)),
+          "reduceSinglePass")
+
+
+def scalarProd(d_C, d_A, d_B, vectorN, elementN, stream=None):
+    """scalarProd sample: d_C[v] = dot(d_A[v], d_B[v]) for vectorN vectors of elementN floats."""
+    check(lib.b200_scalar_prod_async(_dptr(d_C), _dptr(d_A), _dptr(d_B), vectorN, elementN, _stream(stream)),
+          "scalarProd")
+
+
 # ----------------------------------------------------------------------------------------- scan
 def initScan():
     lib.initScan()

@@ -60,6 +60,11 @@ int b200_reduce_f64_async(const double *d_in, size_t n, double *d_out, size_t ou
  * to a double in *d_slot, so partials of mixed types travel in ONE all_gather buffer. */
 int b200_reduce_partial_async(int kind, const void *d_in, size_t n, double *d_slot, b200_stream_t stream);
 
+/* batched dot products (scalarProd sample): d_C[v] = sum_i A[v][i]*B[v][i]; each product rounded to fp32, the sum
+ * kept in fp64 and rounded once, like scalarProdCPU (scalarProd_cpu.cpp:32-46).  8 bytes of traffic per pair. */
+int b200_scalar_prod_async(float *d_C, const float *d_A, const float *d_B, int vectorN, int elementN,
+                           b200_stream_t stream);
+
 /* scan: replaces scanExclusiveShort()/scanExclusiveLarge() (scan.cu:210-266): batchSize independent
  * exclusive +scans of arrayLength u32 each (wrap mod 2^32), single pass, 8 B of traffic per
  * element.  Any arrayLength >= 1 and any batchSize >= 0 (no power-of-two / size caps).

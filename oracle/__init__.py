@@ -48,6 +48,7 @@ def _load():
     lib.oracle_reduce_f32.restype = ctypes.c_float
     lib.oracle_reduce_f64.argtypes = [c_void, u64]
     lib.oracle_reduce_f64.restype = ctypes.c_double
+    lib.oracle_scalar_prod.argtypes = [c_void, c_void, c_void, ctypes.c_int, ctypes.c_int]
     lib.oracle_stable_sort_kv.argtypes = [c_void, c_void, c_void, c_void, u64, u32]
     lib.oracle_merge_sort_host.argtypes = [c_void] * 6 + [u64, u32]
     lib.oracle_validate_sorted_keys.argtypes = [c_void, c_void, u64, u64, u32, u32]
@@ -98,6 +99,15 @@ def reduce(data):
     if data.dtype == np.float64:
         return float(_lib.oracle_reduce_f64(_ptr(data), data.size))
     raise TypeError(data.dtype)
+
+
+def scalar_prod(a, b, vector_n, element_n):
+    a = np.ascontiguousarray(a, dtype=np.float32).reshape(-1)
+    b = np.ascontiguousarray(b, dtype=np.float32).reshape(-1)
+    assert a.size == b.size == vector_n * element_n
+    c = np.empty(vector_n, np.float32)
+    _lib.oracle_scalar_prod(_ptr(c), _ptr(a), _ptr(b), vector_n, element_n)
+    return c
 
 
 def stable_sort_kv(keys, vals, direction=1):
@@ -203,6 +213,8 @@ class _RefGold:
         lib.validateSortedValues.argtypes = [c_void, c_void, c_void, u32, u32]
         lib.validateSortedValues.restype = ctypes.c_int
         lib.fillValues.argtypes = [c_void, u32]
+        if hasattr(lib, "scalarProdCPU"):
+            lib.scalarProdCPU.argtypes = [c_void, c_void, c_void, ctypes.c_int, ctypes.c_int]
 
     def histogram256(self, data):
         data = np.ascontiguousarray(data).view(np.uint8).reshape(-1)
@@ -224,6 +236,13 @@ class _RefGold:
         dst = np.empty_like(src)
         self._lib.scanExclusiveHost(_ptr(dst), _ptr(src), batch, length)
         return dst
+
+    def scalar_prod(self, a, b, vector_n, element_n):
+        a = np.ascontiguousarray(a, dtype=np.float32).reshape(-1)
+        b = np.ascontiguousarray(b, dtype=np.float32).reshape(-1)
+        c = np.empty(vector_n, np.float32)
+        self._lib.scalarProdCPU(_ptr(c), _ptr(a), _ptr(b), vector_n, element_n)
+        return c
 
     def merge_sort_host(self, keys, vals, direction=1):
         keys = np.ascontiguousarray(keys, dtype=np.uint32)

@@ -24,6 +24,7 @@ REF_GOLD = [
     ("2_Concepts_and_Techniques/scan", "scan_gold.cpp"),
     ("0_Introduction/mergeSort", "mergeSort_host.cpp"),
     ("0_Introduction/mergeSort", "mergeSort_validate.cpp"),
+    ("2_Concepts_and_Techniques/scalarProd", "scalarProd_cpu.cpp"),  # "next" row: reduction siblings
 ]
 
 

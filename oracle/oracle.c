@@ -110,6 +110,24 @@ double oracle_reduce_f64(const double *data, uint64_t size)
 }
 
 /* ------------------------------------------------------------------------------------------
+ * scalarProdCPU -- 2_Concepts_and_Techniques/scalarProd/scalarProd_cpu.cpp:32-46
+ * vectorN dot products of elementN floats: the product is a float (float * float), the running sum a
+ * double, the result rounded to float once.
+ * ---------------------------------------------------------------------------------------- */
+void oracle_scalar_prod(float *C, const float *A, const float *B, int vectorN, int elementN)
+{
+    for (int vec = 0; vec < vectorN; vec++) {
+        const float *a = A + (size_t)elementN * vec, *b = B + (size_t)elementN * vec;
+        double       sum = 0;
+        for (int pos = 0; pos < elementN; pos++) {
+            volatile float prod = a[pos] * b[pos]; /* volatile: keep the product a rounded float (no fused multiply-add) */
+            sum += prod;
+        }
+        C[vec] = (float)sum;
+    }
+}
+
+/* ------------------------------------------------------------------------------------------
  * Stable key-value sort: the SPECIFICATION of mergeSort (0_Introduction/mergeSort/mergeSort.cu:
  * 471-537; stable because the tile sort ranks A exclusive / B inclusive, :135-136, and the merges
  * do the same, :304,310).  sortDir != 0 ascending, == 0 descending; ties keep source order in

@@ -559,3 +559,47 @@ def test_unmodified_sample_driver_links_and_passes(prim, name, args):
         assert "Test passed" in r.stdout
     if name == "mergeSort":
         assert "stable!" in r.stdout
+
+
+# ============================================= reduction siblings: same kernels
+@pytest.mark.parametrize("symbol", ["reduce", "reduceSinglePass", "reduceSinglePassMultiBlockCG"])
+def test_single_pass_reduction_siblings(prim, symbol):
+    """threadFenceReduction / reductionMultiBlockCG entry points: float, tolerance of the samples
+    (|gpu - cpu| < 1e-8 * size, threadFenceReduction.cu:479-481) AND the north-star relative 1e-5."""
+    from cuda_samples_b200._lib import lib
+    n = 1 << 20
+    x = oracle.sample_input("reduce_f32", n, 1)
+    d, out = dev(x), torch.full((64,), 3.0, dtype=torch.float32).cuda()
+    torch.cuda.synchronize()
+    getattr(lib, symbol)(n, 128, 64, ctypes.c_void_p(d.data_ptr()), ctypes.c_void_p(out.data_ptr()))
+    torch.cuda.synchronize()
+    o = out.cpu().numpy()
+    want = oracle.reduce(x)
+    assert abs(float(o[0]) - want) < 1e-8 * n and abs(float(o[0]) - want) <= FP32_RTOL * abs(want)
+    assert not o[1:].any()
+    # the samples' multi-pass callers reduce d_odata in place afterwards (threadFenceReduction.cu:247)
+    getattr(lib, symbol)(64, 32, 1, ctypes.c_void_p(out.data_ptr()), ctypes.c_void_p(out.data_ptr()))
+    torch.cuda.synchronize()
+    assert abs(float(out[0]) - want) <= FP32_RTOL * abs(want)
+
+
+@pytest.mark.parametrize("vn,en", [(256, 4096), (1, 1), (3, 7), (5, 100003), (7, 4100), (2, 1 << 22), (1, (1 << 24) + 4),
+                                   (4096, 64), (0, 16)])
+def test_scalar_prod(prim, vn, en):
+    """scalarProd sample (256 x 4096 is its own config): compared with scalarProdCPU's restatement.
+    Products are rounded to float and summed in double on both sides, so the results agree to the last
+    float bit except where the double sums differ in their last bits (different summation order)."""
+    rng = np.random.default_rng(vn * 131 + en)
+    a = rng.random(max(vn * en, 1), dtype=np.float32)[:vn * en]
+    b = (rng.random(max(vn * en, 1), dtype=np.float32)[:vn * en] - 0.25).astype(np.float32)
+    c = torch.full((max(vn, 1),), -7.0, dtype=torch.float32).cuda()
+    prim.scalarProd(c, dev(a) if vn else c, dev(b) if vn else c, vn, en)
+    if vn == 0:
+        return
+    got, want = c.cpu().numpy()[:vn], oracle.scalar_prod(a, b, vn, en)
+    scale = np.maximum(np.abs(want), 1e-30)
+    assert (np.abs(got - want) <= 2.5e-7 * np.maximum(scale, np.sqrt(en) * 1e-3)).all()
+    # the sample's own acceptance test: L1 error < 1e-6 (scalarProd.cu:143-167)
+    if np.abs(want).sum() > 0:
+        assert np.abs(got - want).sum() / np.abs(want).sum() < 1e-6
+    assert (got == want).mean() > 0.9 or vn < 8

@@ -170,3 +170,13 @@ def test_generator_is_counter_based():
     k = oracle.generate("key_tile_unique", 0, 8192, 0, 2048)
     for t in range(8):
         assert np.unique(k[t * 1024:(t + 1) * 1024]).size == 1024
+
+
+@needs_ref
+def test_scalar_prod_restatement_equals_reference_gold():
+    """scalarProd_cpu.cpp:32-46."""
+    rng = np.random.default_rng(12)
+    for vn, en in ((1, 1), (3, 7), (256, 4096), (5, 100003)):
+        a = rng.random(vn * en, dtype=np.float32)
+        b = (rng.random(vn * en, dtype=np.float32) - 0.5).astype(np.float32)
+        assert (oracle.scalar_prod(a, b, vn, en) == oracle.ref.scalar_prod(a, b, vn, en)).all()
