@@ -406,6 +406,15 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
         tile_start = inc - count;
     }
     SORT_TRACE(tile, 3);
+    // First look-back poll: issued now, consumed after the scatter below -- staging the tile in shared memory
+    // needs only tile-local offsets, so it runs while the descriptors of the earlier tiles are on their way.
+    unsigned  first_poll[kLB];
+    long long t_back = (long long)tile - 1;
+    if (tid < kRadix && tile > 0) {
+#pragma unroll
+        for (int j = 0; j < kLB; j++)
+            first_poll[j] = (t_back - j >= 0) ? ld_relaxed_u32(desc + tid + (size_t)(t_back - j) * kRadix) : kDescP;
+    }
     __syncthreads();
     if (tid < kRadix) {
         unsigned woff = 0;
@@ -416,18 +425,32 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
 #pragma unroll
         for (int w = 0; w < kSortWarps; w++)
             S.wc[w][tid].y += tile_start;
+    }
+    __syncthreads();
+
+    // ---- keys and values: to shared memory in digit order ---------------------------------------------------
+#pragma unroll
+    for (int i = 0; i < kSortItems; i++) {
+        const unsigned slot = rank[i] + mywc[op(key[i])].y; // tile-local position
+        S.buf[slot]         = key[i];
+        S.vbuf[slot]        = val[i];
+    }
+    SORT_TRACE(tile, 6);
+
+    // ---- look back: thread d walks over the earlier tiles' counts of digit d, kLB rows per round trip ---------
+    if (tid < kRadix) {
         unsigned excl = 0;
         if (tile > 0) {
-            // thread d walks back over the earlier tiles' counts of digit d.  kLB descriptors are fetched
-            // per round trip (independent loads), then consumed nearest-first.
-            const unsigned *dp = desc + tid;
-            long long       t  = (long long)tile - 1;
-            bool            done = false;
+            const unsigned *dp   = desc + tid;
+            bool            done = false, first = true;
             while (!done) {
                 unsigned d[kLB];
 #pragma unroll
                 for (int j = 0; j < kLB; j++)
-                    d[j] = (t - j >= 0) ? ld_relaxed_u32(dp + (size_t)(t - j) * kRadix) : kDescP;
+                    d[j] = first ? first_poll[j]
+                                 : ((t_back - j >= 0) ? ld_relaxed_u32(dp + (size_t)(t_back - j) * kRadix) : kDescP);
+                first = false;
+                long long t = t_back;
 #pragma unroll
                 for (int j = 0; j < kLB; j++) {
                     if (done || (d[j] >> 30) == 0)
@@ -436,6 +459,7 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
                     t--;
                     done = (d[j] & kDescP) != 0;
                 }
+                t_back = t;
             }
             st_relaxed_u32(desc + (size_t)tile * kRadix + tid, kDescP | (excl + count));
         }
@@ -444,16 +468,7 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
     }
     __syncthreads();
     SORT_TRACE(tile, 5);
-
-    // ---- keys and values: to shared memory in digit order, then out as contiguous runs per digit ----------
-#pragma unroll
-    for (int i = 0; i < kSortItems; i++) {
-        const unsigned slot = rank[i] + mywc[op(key[i])].y; // tile-local position
-        S.buf[slot]         = key[i];
-        S.vbuf[slot]        = val[i];
-    }
-    __syncthreads();
-    SORT_TRACE(tile, 6);
+    // ---- out: every digit's run leaves as contiguous stores ---------------------------------------------------
     if (full) {
 #pragma unroll
         for (int k = 0; k < kSortItems; k++) {
