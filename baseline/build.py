@@ -29,6 +29,9 @@ SAMPLES = {
     "scan": ("2_Concepts_and_Techniques/scan", ["main.cpp", "scan_gold.cpp"], ["scan.cu"]),
     "mergeSort": ("0_Introduction/mergeSort", ["main.cpp", "mergeSort_host.cpp", "mergeSort_validate.cpp"],
                   ["mergeSort.cu"]),
+    # "next" row
+    "sortingNetworks": ("2_Concepts_and_Techniques/sortingNetworks", ["main.cpp", "sortingNetworks_validate.cpp"],
+                        ["bitonicSort.cu", "oddEvenMergeSort.cu"]),
 }
 
 

@@ -19,6 +19,7 @@ RUNS = [
     ("reduction", ["--type=double", "--n=134217728"]),
     ("scan", []),
     ("mergeSort", []),
+    ("sortingNetworks", []),
 ]
 
 

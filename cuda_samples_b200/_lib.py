@@ -34,6 +34,7 @@ SIGNATURES = {
     "b200_scan_total_async": (ci, [vp, vp, sz, vp]),
     "b200_sort_kv_async": (ci, [vp, vp, vp, vp, vp, vp, sz, u32, vp]),
     "b200_partition_kv_async": (ci, [vp, vp, vp, vp, sz, vp, u32, u32, vp, vp]),
+    "b200_segmented_sort_kv_async": (ci, [vp, vp, vp, vp, sz, sz, u32, vp]),
     "b200_generate_async": (ci, [vp, sz, sz, u64, ci, u32, vp]),
     "b200_histogram256_host": (ci, [vp, vp, sz]),
     "b200_histogram64_host": (ci, [vp, vp, sz]),
@@ -58,6 +59,7 @@ SIGNATURES = {
     "mergeSort": (None, [vp, vp, vp, vp, vp, vp, u32, u32]),
     "reduce": (None, [ci, ci, ci, vp, vp]), "reduceSinglePass": (None, [ci, ci, ci, vp, vp]),
     "reduceSinglePassMultiBlockCG": (None, [ci, ci, ci, vp, vp]), "scalarProd": (None, [vp, vp, vp, ci, ci]),
+    "bitonicSort": (u32, [vp, vp, vp, vp, u32, u32, u32]), "oddEvenMergeSort": (None, [vp, vp, vp, vp, u32, u32, u32]),
     "_Z6reduceIiEviiiiPT_S1_": (None, [ci, ci, ci, ci, vp, vp]),
     "_Z6reduceIfEviiiiPT_S1_": (None, [ci, ci, ci, ci, vp, vp]),
     "_Z6reduceIdEviiiiPT_S1_": (None, [ci, ci, ci, ci, vp, vp]),

@@ -187,6 +187,16 @@ def mergeSort(dstKey, dstVal, bufKey, bufVal, srcKey, srcVal, N, sortDir, stream
                                  _dptr(srcVal), N, sortDir, _stream(stream)), "mergeSort")
 
 
+def bitonicSort(d_DstKey, d_DstVal, d_SrcKey, d_SrcVal, batchSize, arrayLength, dir, stream=None):
+    """sortingNetworks sample: batchSize independent key-value sorts of arrayLength pairs (stable, any length)."""
+    check(lib.b200_segmented_sort_kv_async(_dptr(d_DstKey), _dptr(d_DstVal), _dptr(d_SrcKey), _dptr(d_SrcVal),
+                                           batchSize, arrayLength, dir, _stream(stream)), "bitonicSort")
+    return 256
+
+
+oddEvenMergeSort = bitonicSort
+
+
 def partition_kv(dstKey, dstVal, srcKey, srcVal, N, d_splitters, numBuckets, sortDir, d_bucketCounts, stream=None):
     check(lib.b200_partition_kv_async(_dptr(dstKey), _dptr(dstVal), _dptr(srcKey), _dptr(srcVal), N,
                                       _dptr(d_splitters), numBuckets, sortDir, _dptr(d_bucketCounts),

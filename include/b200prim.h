@@ -88,6 +88,12 @@ int b200_partition_kv_async(uint32_t *d_dstKey, uint32_t *d_dstVal, const uint32
                             const uint32_t *d_srcVal, size_t N, const uint32_t *d_splitters, uint32_t numBuckets,
                             uint32_t sortDir, uint32_t *d_bucketCounts, b200_stream_t stream);
 
+/* batched (segmented) stable key-value sort: batchSize independent arrays of arrayLength pairs (the sortingNetworks
+ * sample's bitonicSort / oddEvenMergeSort contract, any length).  src untouched, result in dst. */
+int b200_segmented_sort_kv_async(uint32_t *d_dstKey, uint32_t *d_dstVal, const uint32_t *d_srcKey,
+                                 const uint32_t *d_srcVal, size_t batchSize, size_t arrayLength, uint32_t sortDir,
+                                 b200_stream_t stream);
+
 /* counter-based synthetic data, bit-identical to oracle_generate() (oracle/oracle.c): element i of
  * the stream depends only on (seed, first + i, kind, param), so shards are filled in place. */
 int b200_generate_async(void *d_out, size_t first, size_t n, uint64_t seed, int kind, uint32_t param,

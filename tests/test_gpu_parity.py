@@ -541,7 +541,7 @@ def test_host_variants(prim):
 
 
 # ============================================================== unmodified sample drivers (drop-in)
-@pytest.mark.parametrize("name,args", [("histogram", []), ("scan", []), ("mergeSort", []),
+@pytest.mark.parametrize("name,args", [("histogram", []), ("scan", []), ("mergeSort", []), ("sortingNetworks", []),
                                        ("reduction", ["--type=int"]), ("reduction", ["--type=float"]),
                                        ("reduction", ["--type=double"])])
 def test_unmodified_sample_driver_links_and_passes(prim, name, args):
@@ -661,3 +661,31 @@ def test_entry_points_capture_into_a_cuda_graph_and_replay(prim):
             inputs = fill(seed)
             g.replay()
             check(*inputs)
+
+
+# ================================================= sortingNetworks API: segmented sort
+@pytest.mark.parametrize("batch,L", [(1, 1 << 16), (2, 1 << 15), (256, 256), (257, 64), (16384, 64), (1 << 15, 2),
+                                     (7, 1000), (300, 333), (1, 5)])
+@pytest.mark.parametrize("direction", [1, 0])
+def test_batched_sort_sorting_networks_api(prim, batch, L, direction):
+    """bitonicSort / oddEvenMergeSort contract: every array of the batch sorted on its own; checked against the
+    stable oracle per array and with the sample's own acceptance rules (keys ordered, resKey[j] == srcKey[resVal[j]])."""
+    rng = np.random.default_rng(batch * 7 + L + direction)
+    n = batch * L
+    keys = rng.integers(0, 65536, n, dtype=np.uint32)
+    vals = np.arange(n, dtype=np.uint32)
+    dk, dv = torch.full((n,), -1, dtype=torch.int32).cuda(), torch.full((n,), -1, dtype=torch.int32).cuda()
+    sk, sv = dev(as_i32(keys)), dev(as_i32(vals))
+    assert prim.bitonicSort(dk, dv, sk, sv, batch, L, direction) > 0
+    gk, gv = dk.cpu().numpy().view(np.uint32), dv.cpu().numpy().view(np.uint32)
+    assert (sk.cpu().numpy().view(np.uint32) == keys).all()
+    for a in list(range(min(batch, 3))) + [batch - 1, batch // 2]:
+        wk, wv = oracle.stable_sort_kv(keys[a * L:(a + 1) * L], vals[a * L:(a + 1) * L], direction)
+        assert (gk[a * L:(a + 1) * L] == wk).all() and (gv[a * L:(a + 1) * L] == wv).all()
+    # whole batch: ordered inside every array, pairing intact (validateValues: vals are global indices)
+    g2 = gk.reshape(batch, L).astype(np.int64)
+    if L > 1:
+        d = np.diff(g2, axis=1)
+        assert (d >= 0).all() if direction else (d <= 0).all()
+    assert (keys[gv] == gk).all()
+    assert (np.sort(gv.reshape(batch, L), axis=1) == vals.reshape(batch, L)).all()
