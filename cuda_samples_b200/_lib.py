@@ -47,7 +47,6 @@ SIGNATURES = {
     "b200_host_free": (ci, [vp]),
     "b200_tune_hist_cluster": (ci, [ci]),
     "b200_tune_scan_tma": (ci, [ci]),
-    "b200_tune_scan_window": (ci, [ci]),
     "b200_tune_scan_backoff": (ci, [ci]),
     "b200_tune_sort_lookback": (ci, [ci]),
     # drop-in entry points (the samples' own signatures)

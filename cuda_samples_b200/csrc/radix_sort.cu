@@ -443,7 +443,13 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
         if (tile > 0) {
             const unsigned *dp   = desc + tid;
             bool            done = false, first = true;
+#ifdef B200_SCAN_TRACE
+            unsigned polls = 0, stalls = 0;
+#endif
             while (!done) {
+#ifdef B200_SCAN_TRACE
+                polls++;
+#endif
                 unsigned d[kLB];
 #pragma unroll
                 for (int j = 0; j < kLB; j++)
@@ -453,14 +459,24 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
                 long long t = t_back;
 #pragma unroll
                 for (int j = 0; j < kLB; j++) {
-                    if (done || (d[j] >> 30) == 0)
+                    if (done)
+                        break;
+                    if ((d[j] >> 30) == 0) {
+#ifdef B200_SCAN_TRACE
+                        stalls++;
+#endif
                         break; // not published yet: poll again from this tile
+                    }
                     excl += d[j] & kDescValue;
                     t--;
                     done = (d[j] & kDescP) != 0;
                 }
                 t_back = t;
             }
+#ifdef B200_SCAN_TRACE
+            if (g_sort_trace && threadIdx.x == 0)
+                g_sort_trace[(size_t)tile * 8 + 7] = ((unsigned long long)stalls << 32) | polls;
+#endif
             st_relaxed_u32(desc + (size_t)tile * kRadix + tid, kDescP | (excl + count));
         }
         S.gofs[tid] = __ldg(gbase + tid) + excl - tile_start;

@@ -66,8 +66,9 @@ __device__ __forceinline__ unsigned long long trace_now()
 
 // Warp 0: sum of the aggregates of the tiles before `tile` back to the nearest published prefix.
 // One poll inspects kLookWindow * 32 descriptors (all loads issued together, so a poll costs one L2
-// round trip): the front of published prefixes can only advance by one window per round trip, and a
-// 32-wide window caps the whole scan near 32 tiles * 64 KiB / 0.8 us = 2.6 TB/s on this part.
+// round trip).  Measured on B200 (profiles/r01_scan_window_sweep.log): wider is NOT better -- every
+// in-flight tile polls the same few L2 lines and a 256-wide window slows all memory traffic down
+// (tile loads 5 -> 8 us); 32 is the best flat window.  The TMA kernel uses the two-level scheme below.
 template <int kLookWindow>
 __device__ __forceinline__ unsigned look_back(const unsigned long long *desc, unsigned tile, unsigned first_tile,
                                               unsigned epoch, unsigned backoff_ns = 0)
@@ -261,7 +262,7 @@ __global__ void __launch_bounds__(kScanThreads, 3)
             else {
                 if (lane == 0)
                     st_relaxed_u64(desc + tile, make_desc(epoch, kStA, aggregate));
-                prefix = look_back<4>(desc, tile, first_tile, epoch); // the first tile's prefix already holds the carry
+                prefix = look_back<1>(desc, tile, first_tile, epoch); // the first tile's prefix already holds the carry
                 if (lane == 0)
                     st_relaxed_u64(desc + tile, make_desc(epoch, kStP, prefix + aggregate));
             }
@@ -630,7 +631,6 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
 static bool is_pow2(size_t x) { return x && !(x & (x - 1)); }
 static bool g_scan_use_tma = true;
 static int  g_scan_backoff_ns = 100;
-static int  g_scan_window  = 1; // (register-staged kernel only; the TMA kernel uses the two-level look-back)
 
 } // namespace b200
 
@@ -712,11 +712,6 @@ extern "C" int b200_scan_exclusive_async(uint32_t *d_dst, const uint32_t *d_src,
 extern "C" int b200_tune_scan_tma(int enable)
 {
     g_scan_use_tma = enable != 0;
-    return 0;
-}
-extern "C" int b200_tune_scan_window(int groups)
-{
-    g_scan_window = groups;
     return 0;
 }
 extern "C" int b200_tune_scan_backoff(int ns)

@@ -15,9 +15,7 @@ import cuda_samples_b200 as prim  # noqa: E402
 from cuda_samples_b200._lib import lib  # noqa: E402
 
 N = 1 << 28
-lib.b200_tune_scan_window(int(os.environ.get('SCAN_WINDOW', '8')))
 lib.b200_tune_scan_backoff(int(os.environ.get('SCAN_BACKOFF', '0')))
-print('window groups', os.environ.get('SCAN_WINDOW', '8'), 'backoff', os.environ.get('SCAN_BACKOFF', '0'))
 tiles = N // 8192
 src = torch.empty(N, dtype=torch.int32, device="cuda")
 dst = torch.empty(N, dtype=torch.int32, device="cuda")

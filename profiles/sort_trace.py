@@ -43,7 +43,11 @@ print("pass span %.1f us for %d tiles" % ((t[:, 6].max() - t[:, 0].min()) / 1e3,
 stat("ticket -> keys in registers", t[:, 1] - t[:, 0])
 stat("ranking (16 items)", t[:, 2] - t[:, 1])
 stat("barrier + warp order + publish", t[:, 3] - t[:, 2])
-stat("look-back (digit 0)", t[:, 4] - t[:, 3])
+stat("publish -> staged in smem", t[:, 6] - t[:, 3])
+stat("staged -> look-back done (digit 0)", t[:, 4] - t[:, 6])
 stat("wait for all digits (barrier)", t[:, 5] - t[:, 4])
-stat("scatter to shared memory", t[:, 6] - t[:, 5])
-stat("TOTAL ticket -> staged", t[:, 6] - t[:, 0])
+stat("TOTAL ticket -> all digits resolved", t[:, 5] - t[:, 0])
+raw = trace.cpu().numpy().reshape(tiles, 8)[:, 7]
+polls, stalls = (raw & 0xFFFFFFFF)[mid], (raw >> 32)[mid]
+print("look-back of digit 0: polls per tile mean %.1f p50 %.0f p90 %.0f; of which found an unpublished row: mean %.1f"
+      % (polls.mean(), np.percentile(polls, 50), np.percentile(polls, 90), stalls.mean()))
