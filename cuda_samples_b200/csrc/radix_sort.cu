@@ -30,6 +30,10 @@ constexpr int      kSortItems   = 16;
 constexpr int      kSortCtasPerSm = 4;
 constexpr unsigned kSortTile    = kSortThreads * kSortItems; // 8192 pairs
 constexpr int      kRadix       = 256;
+#ifndef B200_SORT_RANK_MODE
+#define B200_SORT_RANK_MODE 2
+#endif
+constexpr int      kRankMode    = B200_SORT_RANK_MODE; // 0: ATOMS.OR match, 1: ballot match, 2: alternate per item
 constexpr unsigned kDescA = 1u << 30, kDescP = 2u << 30, kDescValue = (1u << 30) - 1;
 
 #ifdef B200_SCAN_TRACE
@@ -298,12 +302,16 @@ __global__ void __launch_bounds__(kHist4Threads, 1)
 
 // ---------------------------------------------------------------------------------------------------
 // One scatter pass (chained scan over tiles).
-// Ranking inside a warp: per item, every lane ORs its lane bit into a warp-private shared word of its
-// digit (one ATOMS.OR), reads the word back -> the lanes holding the same digit, and the running
-// count of that digit kept next to it (one 64-bit shared load fetches both).  rank = count + number
-// of lower lanes in the mask; the lowest lane of each group writes {0, count + group size} back.
-// Measured on B200 (profiles/microbench/match_bench.cu): 3.4x cheaper than eight ballots and 8.4x
-// cheaper than MATCH.ANY.  Index order inside the tile = (warp, item, lane), so ranks are stable.
+// Ranking inside a warp needs, per item, the lanes holding the same digit.  Two ways, alternated per item so
+// that the shared-memory pipe and the ALU pipes share the load (measured: 7.69 ms all-shared, 7.46 ms all-ballot,
+// 7.43 ms alternated for 2^28 pairs):
+//   shared  every lane ORs its lane bit into a warp-private word of its digit (one ATOMS.OR) and reads the word
+//           back together with the running count kept next to it (one 64-bit load); the group's lowest lane
+//           writes {0, count + group size} back.  In isolation 3.4x cheaper than eight ballots and 8.4x cheaper
+//           than MATCH.ANY (profiles/microbench/match_bench.cu).
+//   ballot  eight vote.ballot build the mask in registers; only the group's lowest lane touches the counter.
+// rank = count so far + number of lower lanes in the mask.  Index order inside the tile = (warp, item, lane),
+// so ranks are stable.  (What bounds the pass is analysed in DESIGN.md section 6.)
 // ---------------------------------------------------------------------------------------------------
 template <bool kBucket, int kLB>
 __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
@@ -357,15 +365,31 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
 #pragma unroll
     for (int i = 0; i < kSortItems; i++) {
         uint2 *slot = mywc + op(key[i]);
-        atomicOr(&slot->x, 1u << lane);
-        __syncwarp();
-        const uint2    w     = lds_u2(slot); // {lanes with this digit, count so far}
-        const unsigned below = w.x & lt;
-        rank[i]              = w.y + __popc(below);
-        __syncwarp();
-        if (below == 0) // lowest lane of the group: clear the mask, advance the count
-            *slot = make_uint2(0u, w.y + __popc(w.x));
-        __syncwarp();
+        if (kRankMode == 0 || (kRankMode == 2 && (i & 1))) {
+            // shared-memory match: OR the lane bit into the digit's word, read {mask, count} back
+            atomicOr(&slot->x, 1u << lane);
+            __syncwarp();
+            const uint2    w     = lds_u2(slot); // {lanes with this digit, count so far}
+            const unsigned below = w.x & lt;
+            rank[i]              = w.y + __popc(below);
+            __syncwarp();
+            if (below == 0) // lowest lane of the group: clear the mask, advance the count
+                *slot = make_uint2(0u, w.y + __popc(w.x));
+            __syncwarp();
+        }
+        else {
+            // register match: eight ballots build the mask (ALU only), the group's lowest lane bumps the count
+            const unsigned mask   = match_digit(op(key[i]));
+            const unsigned below  = mask & lt;
+            unsigned       pre    = 0;
+            if (below == 0) {
+                pre     = slot->y;
+                slot->y = pre + __popc(mask);
+            }
+            pre     = __shfl_sync(0xffffffffu, pre, __ffs(mask) - 1);
+            rank[i] = pre + __popc(below);
+            __syncwarp();
+        }
     }
 
     SORT_TRACE(tile, 2);
