@@ -40,6 +40,13 @@ def _compile(src, obj, verbose):
 
 def build(force=False, verbose=False, trace=False):
     global OBJ, LIB, FLAGS
+    extra = os.environ.get("B200_EXTRA_FLAGS")
+    if extra:  # tuning variants: B200_EXTRA_FLAGS="-DX=1 ..." B200_VARIANT=name -> variants/lib_<name>.so
+        name = os.environ.get("B200_VARIANT", "variant")
+        OBJ = os.path.join(HERE, "build_" + name)
+        os.makedirs(os.path.join(HERE, "variants"), exist_ok=True)
+        LIB = os.path.join(HERE, "variants", "lib_%s.so" % name)
+        FLAGS = FLAGS + extra.split()
     if trace:  # debug variant with per-tile pipeline timestamps (profiles/scan_trace.py)
         OBJ = os.path.join(HERE, "build_trace")
         LIB = os.path.join(HERE, "libb200prim_trace.so")

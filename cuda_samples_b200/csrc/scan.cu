@@ -359,14 +359,18 @@ __device__ __forceinline__ bool window32(const unsigned long long *desc, long lo
 // Every CTA draws exactly one out-of-range ticket, so the draw numbered tiles+grid-1 is the last one and
 // its owner re-arms {epoch+1, ticket 0} for the next launch.
 // ---------------------------------------------------------------------------------------------------
-constexpr int      kTmaStages    = 6;
-constexpr int      kTmaAhead     = 3;                   // phase A runs this many tiles ahead of phase B
+// Tile geometry is a template parameter <kTmaRows 16-byte vectors per thread, kTmaStages, kTmaAhead>; measured for
+// one 2^28-element array (profiles/r01_scan_geometry_sweep.log): 24 KiB x 9 stages 520 us, 32 KiB x 6 434 us,
+// 40 KiB x 5 (phase A 3 ahead) 395 us, 48 KiB x 4 413 us, 64 KiB x 3 477 us.  Short arrays (a few tiles each)
+// prefer 32 KiB tiles that divide them evenly (16384 arrays of 16384: 344 us vs 396 us).
 constexpr int      kTmaLookWarps = 2;
 constexpr int      kTmaThreads   = kScanThreads + 32 * (1 + kTmaLookWarps); // 16 scan + 1 producer + 2 look-back
 constexpr unsigned kTileEnd      = 0xffffffffu;
 
+template <int kTmaRows, int kTmaStages>
 struct ScanTmaSmem {
-    unsigned buf[kTmaStages][kScanTile];    // 6 x 32 KiB
+    static constexpr unsigned kTmaTile = kScanThreads * kTmaRows * 4;
+    unsigned buf[kTmaStages][kTmaTile];     // tiles in flight / being scanned
     uint64_t full[kTmaStages];              // producer  -> all     : tile landed (tx bytes) / END marker
     uint64_t agg_ready[kTmaStages];         // scan warps -> look-back: the 16 warp totals are in
     uint64_t prefix_ready[kTmaStages];      // look-back -> scan warps: exclusive tile prefix is in
@@ -383,12 +387,18 @@ __device__ __forceinline__ void mbar_arrive(uint64_t *bar)
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
+template <int kTmaRows, int kTmaStages, int kTmaAhead>
 __global__ void __launch_bounds__(kTmaThreads, 1)
     scan_tma_kernel(unsigned *dst, const unsigned *src, const ScanParams p, unsigned long long *state,
                     unsigned long long *desc)
 {
+    // the end marker is passed on through agg_ready of the stages of indices a, a+1: their previous phases must
+    // have been consumed by then, which holds when the ring is at least two stages longer than the look-ahead
+    static_assert(kTmaStages >= kTmaAhead + 2, "stage ring too short for the phase-A look-ahead");
+    typedef ScanTmaSmem<kTmaRows, kTmaStages> Smem;
+    constexpr unsigned kTmaTile = Smem::kTmaTile;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    ScanTmaSmem   &S    = *reinterpret_cast<ScanTmaSmem *>(smem_raw);
+    Smem          &S    = *reinterpret_cast<Smem *>(smem_raw);
     const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
     if (threadIdx.x == 0) {
@@ -434,9 +444,9 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
                 break;
             }
             const unsigned a = ticket / p.tpa, t = ticket - a * p.tpa;
-            const size_t   off    = (size_t)a * p.L + (size_t)t * kScanTile;
-            const size_t   remain = p.L - (size_t)t * kScanTile;
-            const unsigned count  = remain < kScanTile ? (unsigned)remain : kScanTile;
+            const size_t   off    = (size_t)a * p.L + (size_t)t * kTmaTile;
+            const size_t   remain = p.L - (size_t)t * kTmaTile;
+            const unsigned count  = remain < kTmaTile ? (unsigned)remain : kTmaTile;
             S.tile[s]  = ticket;
             S.count[s] = count;
             S.epoch[s] = epoch;
@@ -546,8 +556,8 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
             const unsigned count = S.count[s];
             unsigned       sum   = 0;
 #pragma unroll
-            for (int r = 0; r < kScanRows; r++) {
-                const unsigned e = warp * (kScanRows * 128) + r * 128 + lane * 4;
+            for (int r = 0; r < kTmaRows; r++) {
+                const unsigned e = warp * (kTmaRows * 128) + r * 128 + lane * 4;
                 uint4          v = *reinterpret_cast<const uint4 *>(&S.buf[s][e]);
                 if (e < count) // ragged last tile of an array (count is a multiple of 4 here)
                     sum += (v.x + v.y) + (v.z + v.w);
@@ -577,11 +587,11 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
         const unsigned count = S.count[s];
         if (threadIdx.x == 0)
             SCAN_TRACE(S.tile[s], 5);
-        uint4          v[kScanRows];
-        unsigned       ebase[kScanRows], tot[kScanRows], inc[kScanRows];
+        uint4          v[kTmaRows];
+        unsigned       ebase[kTmaRows], tot[kTmaRows], inc[kTmaRows];
 #pragma unroll
-        for (int r = 0; r < kScanRows; r++) {
-            ebase[r] = warp * (kScanRows * 128) + r * 128 + lane * 4;
+        for (int r = 0; r < kTmaRows; r++) {
+            ebase[r] = warp * (kTmaRows * 128) + r * 128 + lane * 4;
             v[r]     = *reinterpret_cast<const uint4 *>(&S.buf[s][ebase[r]]);
             if (ebase[r] >= count)
                 v[r] = make_uint4(0, 0, 0, 0);
@@ -591,7 +601,7 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1)
 #pragma unroll
-            for (int r = 0; r < kScanRows; r++) {
+            for (int r = 0; r < kTmaRows; r++) {
                 unsigned t = __shfl_up_sync(0xffffffffu, inc[r], d);
                 if (lane >= d)
                     inc[r] += t;
@@ -612,9 +622,9 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
         if (lane == 0)
             mbar_arrive(&S.scanned[s]);
         const unsigned ab = tile_b / p.tpa;
-        unsigned      *out = dst + (size_t)ab * p.L + (size_t)(tile_b - ab * p.tpa) * kScanTile;
+        unsigned      *out = dst + (size_t)ab * p.L + (size_t)(tile_b - ab * p.tpa) * kTmaTile;
 #pragma unroll
-        for (int r = 0; r < kScanRows; r++) {
+        for (int r = 0; r < kTmaRows; r++) {
             const unsigned e0 = run + (inc[r] - tot[r]);
             run += __shfl_sync(0xffffffffu, inc[r], 31);
             uint4 o;
@@ -684,20 +694,43 @@ extern "C" int b200_scan_exclusive_async(uint32_t *d_dst, const uint32_t *d_src,
     B200_TRY((cudaError_t)ensure(c->scan, 16 + 8 * ndesc, stream));
     unsigned           *state = reinterpret_cast<unsigned *>(c->scan.ptr);
     unsigned long long *desc  = reinterpret_cast<unsigned long long *>(reinterpret_cast<char *>(c->scan.ptr) + 16);
-    const bool tma_ok = large && p.tpa > 1 && (L % 4) == 0 && g_scan_use_tma &&
+    const bool tma_ok = large && L > kScanTile && (L % 4) == 0 && g_scan_use_tma &&
                         ((((uintptr_t)d_dst) | ((uintptr_t)d_src)) & 15) == 0;
     if (tma_ok) {
+        // long arrays: 40 KiB tiles x 5 stages; arrays of a few tiles: 32 KiB x 6 (divides powers of two evenly)
+        const bool     big  = L >= (1u << 20);
+        const unsigned tile = big ? kScanThreads * 5 * 4 : kScanThreads * 4 * 4;
+        const size_t   tpa_t = (L + tile - 1) / tile;
+        if (tpa_t * batch > 0xfffffff0ull)
+            return (int)cudaErrorInvalidValue;
+        p.tpa       = (unsigned)tpa_t;
+        p.num_tiles = (unsigned)(tpa_t * batch);
+        const size_t nd = (size_t)p.num_tiles + batch * ((tpa_t + 31) / 32);
+        B200_TRY((cudaError_t)ensure(c->scan, 16 + 8 * nd, stream));
+        state = reinterpret_cast<unsigned *>(c->scan.ptr);
+        desc  = reinterpret_cast<unsigned long long *>(reinterpret_cast<char *>(c->scan.ptr) + 16);
         unsigned grid = (unsigned)c->num_sms; // one persistent CTA per SM
         if (grid > p.num_tiles)
             grid = p.num_tiles;
         auto *st64 = reinterpret_cast<unsigned long long *>(state);
-        static bool prepared = false;
-        if (!prepared) {
-            B200_TRY(cudaFuncSetAttribute(scan_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          (int)sizeof(ScanTmaSmem)));
-            prepared = true;
+        if (big) {
+            static bool prepared = false;
+            if (!prepared) {
+                B200_TRY(cudaFuncSetAttribute(scan_tma_kernel<5, 5, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)sizeof(ScanTmaSmem<5, 5>)));
+                prepared = true;
+            }
+            scan_tma_kernel<5, 5, 3><<<grid, kTmaThreads, sizeof(ScanTmaSmem<5, 5>), stream>>>(d_dst, d_src, p, st64, desc);
         }
-        scan_tma_kernel<<<grid, kTmaThreads, sizeof(ScanTmaSmem), stream>>>(d_dst, d_src, p, st64, desc);
+        else {
+            static bool prepared = false;
+            if (!prepared) {
+                B200_TRY(cudaFuncSetAttribute(scan_tma_kernel<4, 6, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)sizeof(ScanTmaSmem<4, 6>)));
+                prepared = true;
+            }
+            scan_tma_kernel<4, 6, 3><<<grid, kTmaThreads, sizeof(ScanTmaSmem<4, 6>), stream>>>(d_dst, d_src, p, st64, desc);
+        }
     }
     else if (large)
         scan_kernel<true><<<p.num_tiles, kScanThreads, 0, stream>>>(d_dst, d_src, p, state, desc);
@@ -734,7 +767,7 @@ extern "C" int b200_scan_reserve(size_t n)
     DeviceCtx *c  = ctx(&st);
     if (!c)
         return st;
-    const size_t tiles = (n + kScanTile - 1) / kScanTile;
+    const size_t tiles = (n + kScanTile - 1) / kScanTile; // (40 KiB tiles need fewer)
     B200_TRY((cudaError_t)ensure(c->scan, 16 + 8 * (tiles + tiles / 32 + 64), 0));
     return 0;
 }
