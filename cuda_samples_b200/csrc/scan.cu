@@ -344,7 +344,7 @@ __device__ __forceinline__ bool window32(const unsigned long long *desc, long lo
 
 // ---------------------------------------------------------------------------------------------------
 // Chained scan, persistent + TMA-staged (the hot case: arrays spanning several tiles, 16-byte aligned).
-// One CTA per SM, kTmaStages tiles of 32 KiB in flight in shared memory, four warp roles that only
+// One CTA per SM, kTmaStages tiles (32 or 40 KiB) in flight in shared memory, four warp roles that only
 // meet through mbarriers (no CTA-wide barrier anywhere in the steady state):
 //   producer  (1 lane)   draws {epoch|ticket} with ONE 64-bit atomicAdd, streams the tile in with
 //                        cp.async.bulk (1-D TMA, SASS UBLKCP) and, once the scan warps have overwritten
@@ -353,8 +353,8 @@ __device__ __forceinline__ bool window32(const unsigned long long *desc, long lo
 //                        tile's total publishes the look-back aggregate at once, long before the tile is
 //                        scanned.  Phase B on tile k: warp-striped scan in shared memory, seeded with the
 //                        tile prefix, conflict-free 16-byte shared accesses;
-//   look-back warps (2)  alternate over the CTA's tiles: wait for the tile's total, walk the descriptors
-//                        back (128 per poll), publish the inclusive prefix, hand the exclusive prefix to
+//   look-back warps (2)  alternate over the CTA's tiles: wait for the tile's total, two-level look-back
+//                        (own chunk of 32 tiles, then chunk descriptors), publish the inclusive prefix, hand the exclusive prefix to
 //                        the scan warps.  Look-back latency is off the scan warps' critical path.
 // Every CTA draws exactly one out-of-range ticket, so the draw numbered tiles+grid-1 is the last one and
 // its owner re-arms {epoch+1, ticket 0} for the next launch.
