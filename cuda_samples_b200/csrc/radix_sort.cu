@@ -24,16 +24,25 @@
 
 namespace b200 {
 
-constexpr int      kSortThreads = 256;
+#ifndef B200_SORT_THREADS // tile geometry: overridable for sweeps (profiles/sort_variants.sh)
+#define B200_SORT_THREADS 256
+#endif
+#ifndef B200_SORT_ITEMS
+#define B200_SORT_ITEMS 16
+#endif
+#ifndef B200_SORT_CTAS
+#define B200_SORT_CTAS 4
+#endif
+constexpr int      kSortThreads = B200_SORT_THREADS;
 constexpr int      kSortWarps   = kSortThreads / 32;
-constexpr int      kSortItems   = 16;
-constexpr int      kSortCtasPerSm = 4;
-constexpr unsigned kSortTile    = kSortThreads * kSortItems; // 8192 pairs
+constexpr int      kSortItems   = B200_SORT_ITEMS;
+constexpr int      kSortCtasPerSm = B200_SORT_CTAS;
+constexpr unsigned kSortTile    = kSortThreads * kSortItems; // pairs per tile (4096)
+static_assert(kSortThreads >= 256 && kSortTile <= 65536, "digit owners are threads 0..255; rank | digit << 16");
 constexpr int      kRadix       = 256;
 #ifndef B200_SORT_RANK_MODE
-#define B200_SORT_RANK_MODE 2
+#define B200_SORT_RANK_MODE 0 // 0: the group's lowest lane bumps the digit counter with ATOMS.ADD; 1: with LDS + STS
 #endif
-constexpr int      kRankMode    = B200_SORT_RANK_MODE; // 0: ATOMS.OR match, 1: ballot match, 2: alternate per item
 constexpr unsigned kDescA = 1u << 30, kDescP = 2u << 30, kDescValue = (1u << 30) - 1;
 
 #ifdef B200_SCAN_TRACE
@@ -51,12 +60,12 @@ __device__ __forceinline__ unsigned long long sort_now()
 #define SORT_TRACE(tile, slot) do { } while (0)
 #endif
 
-// shared memory of the pass kernel (dynamic, > 48 KiB)
+// shared memory of the pass kernel (dynamic)
 struct SortSmem {
     unsigned buf[kSortTile];              // keys in digit order
     unsigned vbuf[kSortTile];             // values in digit order
-    uint2    wc[kSortWarps][kRadix];      // per warp and digit: {lane mask of the current item, running count}
-                                          // -> .y becomes the warp's scatter base for the digit
+    unsigned wcnt[kSortWarps][kRadix];    // per warp and digit: running count while ranking, then the warp's
+                                          // tile-local scatter base for the digit (plain u32: all 32 banks)
     unsigned gofs[kRadix];                // global index of a digit's first slot minus its tile-local start
     unsigned wsum[kRadix / 32];
     unsigned splitters[kRadix];
@@ -85,23 +94,34 @@ template <bool kBucket> struct DigitOp {
     }
 };
 
-__device__ __forceinline__ uint2 lds_u2(const uint2 *p)
+// lanes of the warp holding the same 8-bit digit (one ballot per bit, registers only)
+// per bit: test -> predicate, ballot, predicate -> 0/-1, mask &= ~(vote ^ that): 4 issue slots (the compiler's
+// own sequence for the C expression spends 6: it shifts and re-compares to form the predicate)
+template <int B> __device__ __forceinline__ void match_bit(unsigned &mask, unsigned d)
 {
-    uint2 r;
-    asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "r"(smem_u32(p)) : "memory");
-    return r;
+    asm volatile("{\n\t"
+                 ".reg .pred p;\n\t"
+                 ".reg .b32 t, v;\n\t"
+                 "and.b32 t, %1, %2;\n\t"
+                 "setp.ne.u32 p, t, 0;\n\t"
+                 "vote.sync.ballot.b32 v, p, 0xffffffff;\n\t"
+                 "selp.b32 t, -1, 0, p;\n\t"
+                 "lop3.b32 %0, %0, v, t, 0x90;\n\t"
+                 "}"
+                 : "+r"(mask)
+                 : "r"(d), "n"(1 << B));
 }
-
-// lanes of the warp holding the same 8-bit digit (ballot per bit) -- kept for reference / the micro-benchmark
 __device__ __forceinline__ unsigned match_digit(unsigned d)
 {
     unsigned mask = 0xffffffffu;
-#pragma unroll
-    for (int b = 0; b < 8; b++) {
-        const bool     bit  = (d >> b) & 1u;
-        const unsigned vote = __ballot_sync(0xffffffffu, bit);
-        mask &= bit ? vote : ~vote;
-    }
+    match_bit<0>(mask, d);
+    match_bit<1>(mask, d);
+    match_bit<2>(mask, d);
+    match_bit<3>(mask, d);
+    match_bit<4>(mask, d);
+    match_bit<5>(mask, d);
+    match_bit<6>(mask, d);
+    match_bit<7>(mask, d);
     return mask;
 }
 
@@ -302,16 +322,19 @@ __global__ void __launch_bounds__(kHist4Threads, 1)
 
 // ---------------------------------------------------------------------------------------------------
 // One scatter pass (chained scan over tiles).
-// Ranking inside a warp needs, per item, the lanes holding the same digit.  Two ways, alternated per item so
-// that the shared-memory pipe and the ALU pipes share the load (measured: 7.69 ms all-shared, 7.46 ms all-ballot,
-// 7.43 ms alternated for 2^28 pairs):
-//   shared  every lane ORs its lane bit into a warp-private word of its digit (one ATOMS.OR) and reads the word
-//           back together with the running count kept next to it (one 64-bit load); the group's lowest lane
-//           writes {0, count + group size} back.  In isolation 3.4x cheaper than eight ballots and 8.4x cheaper
-//           than MATCH.ANY (profiles/microbench/match_bench.cu).
-//   ballot  eight vote.ballot build the mask in registers; only the group's lowest lane touches the counter.
-// rank = count so far + number of lower lanes in the mask.  Index order inside the tile = (warp, item, lane),
-// so ranks are stable.  (What bounds the pass is analysed in DESIGN.md section 6.)
+// What bounds this kernel is the SM's load/store data pipe (ncu: l1tex__data_pipe_lsu_wavefronts at 82 % of
+// peak in the first version, issue slots at 33 %), so the kernel is written to spend as few shared/global
+// WAVEFRONTS per pair as possible and pays for that with ALU work:
+//   * ranking inside a warp: the lanes holding the same digit are found with eight vote.ballot (registers only);
+//     the group's lowest lane then bumps a warp-private u32 counter with ONE shared atomic that returns the
+//     count so far (the first version used a 64-bit {mask, count} word per digit: an ATOMS.OR, a 64-bit load
+//     and a 64-bit store per item on 16 of the 32 banks);
+//   * rank = count so far + number of lower lanes in the mask.  Index order inside the tile = (warp, item, lane),
+//     so ranks are stable;
+//   * the per-digit sweep over the warps reads the eight counters once, keeps them in registers across the
+//     block scan and writes the eight scatter bases once;
+//   * keys go to shared memory as soon as the bases are known; the values are loaded only then (their latency
+//     hides behind the look-back), so that at most 32 payload registers are live and nothing spills.
 // ---------------------------------------------------------------------------------------------------
 template <bool kBucket, int kLB>
 __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
@@ -327,8 +350,11 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
 
     if (tid == 0)
         S.tile = atomicAdd(ticket, 1u);
-    for (int i = tid; i < kSortWarps * kRadix; i += kSortThreads)
-        (&S.wc[0][0])[i] = make_uint2(0u, 0u);
+    {
+        uint4 *z = reinterpret_cast<uint4 *>(&S.wcnt[0][0]);
+        for (int i = tid; i < kSortWarps * kRadix / 4; i += kSortThreads)
+            z[i] = make_uint4(0u, 0u, 0u, 0u);
+    }
     if (kBucket && tid < nspl)
         S.splitters[tid] = splitters[tid];
     __syncthreads();
@@ -339,7 +365,7 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
     const bool       full  = valid == kSortTile;
     DigitOp<kBucket> op{shift, flip, nspl, S.splitters};
 
-    // ---- load keys (warp-striped: item i of lane l is element warp*512 + i*32 + l of the tile) --------
+    // ---- load keys (warp-striped: item i of lane l is element warp*(items*32) + i*32 + l of the tile) ----
     unsigned       key[kSortItems];
     const unsigned wbase = warp * (kSortItems * 32) + lane;
     const unsigned pad   = ~flip; // (pad ^ flip) = 0xffffffff: last digit in every pass, ranks after all valid keys
@@ -354,9 +380,9 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
             key[i] = (wbase + i * 32 < valid) ? __ldg(kin + base + wbase + i * 32) : pad;
     }
 
-    // ---- rank inside the warp, in index order -----------------------------------------------------------
-    unsigned rank[kSortItems];
-    uint2   *mywc = S.wc[warp];
+    // ---- rank inside the warp, in index order ------------------------------------------------------------
+    unsigned  rank[kSortItems]; // rank | digit << 16
+    unsigned *mycnt = S.wcnt[warp];
 #ifdef B200_SCAN_TRACE
     if (key[kSortItems - 1] == 0x12345678u)
         SORT_TRACE(tile, 7); // (forces the last key load to complete before slot 1 is stamped)
@@ -364,59 +390,45 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
 #endif
 #pragma unroll
     for (int i = 0; i < kSortItems; i++) {
-        uint2 *slot = mywc + op(key[i]);
-        if (kRankMode == 0 || (kRankMode == 2 && (i & 1))) {
-            // shared-memory match: OR the lane bit into the digit's word, read {mask, count} back
-            atomicOr(&slot->x, 1u << lane);
-            __syncwarp();
-            const uint2    w     = lds_u2(slot); // {lanes with this digit, count so far}
-            const unsigned below = w.x & lt;
-            rank[i]              = w.y + __popc(below);
-            __syncwarp();
-            if (below == 0) // lowest lane of the group: clear the mask, advance the count
-                *slot = make_uint2(0u, w.y + __popc(w.x));
-            __syncwarp();
+        const unsigned d     = op(key[i]);
+        const unsigned mask  = match_digit(d);
+        const unsigned below = mask & lt;
+        unsigned       pre   = 0;
+        if (below == 0) {
+#if B200_SORT_RANK_MODE == 1
+            pre      = mycnt[d]; // groups of one round hold distinct digits: no atomicity needed inside a warp
+            mycnt[d] = pre + __popc(mask);
+#else
+            pre = atomicAdd(mycnt + d, (unsigned)__popc(mask));
+#endif
         }
-        else {
-            // register match: eight ballots build the mask (ALU only), the group's lowest lane bumps the count
-            const unsigned mask   = match_digit(op(key[i]));
-            const unsigned below  = mask & lt;
-            unsigned       pre    = 0;
-            if (below == 0) {
-                pre     = slot->y;
-                slot->y = pre + __popc(mask);
-            }
-            pre     = __shfl_sync(0xffffffffu, pre, __ffs(mask) - 1);
-            rank[i] = pre + __popc(below);
-            __syncwarp();
-        }
+        pre     = __shfl_sync(0xffffffffu, pre, __ffs(mask) - 1);
+        rank[i] = (pre + __popc(below)) | (d << 16);
+#if B200_SORT_RANK_MODE == 1
+        __syncwarp();
+#endif
     }
-
     SORT_TRACE(tile, 2);
-    // values: issue the loads now, they are consumed after the look-back
-    unsigned val[kSortItems];
-    if (full) {
-#pragma unroll
-        for (int i = 0; i < kSortItems; i++)
-            val[i] = __ldg(vin + base + wbase + i * 32);
-    }
-    else {
-#pragma unroll
-        for (int i = 0; i < kSortItems; i++)
-            val[i] = (wbase + i * 32 < valid) ? __ldg(vin + base + wbase + i * 32) : 0u;
-    }
     __syncthreads();
 
-    // ---- per digit: order the warps, publish the tile count, look back --------------------------------
-    unsigned count = 0, tile_start = 0;
+    // ---- per digit: order the warps, publish the tile count, first look-back poll -----------------------
+    unsigned  count = 0, tile_start = 0;
+    unsigned  c[kSortWarps];
+    unsigned  first_poll[kLB];
+    long long t_back = (long long)tile - 1;
     if (tid < kRadix) {
 #pragma unroll
         for (int w = 0; w < kSortWarps; w++) {
-            unsigned t     = S.wc[w][tid].y;
-            S.wc[w][tid].y = count;
-            count += t;
+            c[w] = S.wcnt[w][tid];
+            count += c[w];
         }
         st_relaxed_u32(desc + (size_t)tile * kRadix + tid, (tile == 0 ? kDescP : kDescA) | count);
+        // issued now, consumed after the staging below (which needs only tile-local offsets)
+        if (tile > 0) {
+#pragma unroll
+            for (int j = 0; j < kLB; j++)
+                first_poll[j] = (t_back - j >= 0) ? ld_relaxed_u32(desc + tid + (size_t)(t_back - j) * kRadix) : kDescP;
+        }
         // exclusive scan of the 256 counts -> where each digit starts inside the tile
         unsigned inc = count;
 #pragma unroll
@@ -430,34 +442,38 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
         tile_start = inc - count;
     }
     SORT_TRACE(tile, 3);
-    // First look-back poll: issued now, consumed after the scatter below -- staging the tile in shared memory
-    // needs only tile-local offsets, so it runs while the descriptors of the earlier tiles are on their way.
-    unsigned  first_poll[kLB];
-    long long t_back = (long long)tile - 1;
-    if (tid < kRadix && tile > 0) {
-#pragma unroll
-        for (int j = 0; j < kLB; j++)
-            first_poll[j] = (t_back - j >= 0) ? ld_relaxed_u32(desc + tid + (size_t)(t_back - j) * kRadix) : kDescP;
-    }
     __syncthreads();
     if (tid < kRadix) {
-        unsigned woff = 0;
 #pragma unroll
         for (int w = 0; w < kRadix / 32; w++)
-            woff += (w < (int)warp) ? S.wsum[w] : 0u;
-        tile_start += woff;
+            tile_start += (w < (int)warp) ? S.wsum[w] : 0u;
+        unsigned run = tile_start;
 #pragma unroll
-        for (int w = 0; w < kSortWarps; w++)
-            S.wc[w][tid].y += tile_start;
+        for (int w = 0; w < kSortWarps; w++) {
+            S.wcnt[w][tid] = run;
+            run += c[w];
+        }
     }
     __syncthreads();
 
-    // ---- keys and values: to shared memory in digit order ---------------------------------------------------
+    // ---- keys to shared memory in digit order; the slot replaces the rank -----------------------------------
 #pragma unroll
     for (int i = 0; i < kSortItems; i++) {
-        const unsigned slot = rank[i] + mywc[op(key[i])].y; // tile-local position
+        const unsigned slot = (rank[i] & 0xffffu) + mycnt[rank[i] >> 16]; // tile-local position
         S.buf[slot]         = key[i];
-        S.vbuf[slot]        = val[i];
+        rank[i]             = slot;
+    }
+    // ---- values: loaded now, in flight during the look-back ------------------------------------------------
+    unsigned val[kSortItems];
+    if (full) {
+#pragma unroll
+        for (int i = 0; i < kSortItems; i++)
+            val[i] = __ldg(vin + base + wbase + i * 32);
+    }
+    else {
+#pragma unroll
+        for (int i = 0; i < kSortItems; i++)
+            val[i] = (wbase + i * 32 < valid) ? __ldg(vin + base + wbase + i * 32) : 0u;
     }
     SORT_TRACE(tile, 6);
 
@@ -506,6 +522,9 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
         S.gofs[tid] = __ldg(gbase + tid) + excl - tile_start;
         SORT_TRACE(tile, 4);
     }
+#pragma unroll
+    for (int i = 0; i < kSortItems; i++)
+        S.vbuf[rank[i]] = val[i];
     __syncthreads();
     SORT_TRACE(tile, 5);
     // ---- out: every digit's run leaves as contiguous stores ---------------------------------------------------
