@@ -25,13 +25,13 @@
 namespace b200 {
 
 #ifndef B200_SORT_THREADS // tile geometry: overridable for sweeps (profiles/sort_variants.sh)
-#define B200_SORT_THREADS 256
+#define B200_SORT_THREADS 512
 #endif
 #ifndef B200_SORT_ITEMS
 #define B200_SORT_ITEMS 16
 #endif
 #ifndef B200_SORT_CTAS
-#define B200_SORT_CTAS 4
+#define B200_SORT_CTAS 2
 #endif
 constexpr int      kSortThreads = B200_SORT_THREADS;
 constexpr int      kSortWarps   = kSortThreads / 32;
