@@ -15,7 +15,8 @@ import cuda_samples_b200 as prim  # noqa: E402
 from cuda_samples_b200._lib import lib  # noqa: E402
 
 N = 1 << 28
-tiles = (N + 4095) // 4096
+TILE = int(os.environ.get("B200_SORT_TILE", "8192"))
+tiles = (N + TILE - 1) // TILE
 sk = torch.empty(N, dtype=torch.int32, device="cuda")
 sv = torch.arange(N, dtype=torch.int32, device="cuda")
 dk, dv, bk, bv = (torch.empty(N, dtype=torch.int32, device="cuda") for _ in range(4))
