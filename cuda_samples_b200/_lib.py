@@ -43,6 +43,15 @@ SIGNATURES = {
     "b200_reduce_f64_host": (ci, [vp, sz, vp]),
     "b200_scan_exclusive_host": (ci, [vp, vp, sz, sz]),
     "b200_sort_kv_host": (ci, [vp, vp, vp, vp, sz, u32]),
+    "b200_p2p_window_create": (ci, [ctypes.c_char_p]),
+    "b200_p2p_connect": (ci, [ci, ci, ctypes.c_char_p]),
+    "b200_p2p_disconnect": (ci, []),
+    "b200_p2p_world": (ci, []),
+    "b200_p2p_errors": (ci, [ctypes.POINTER(ctypes.c_ulonglong)]),
+    "b200_p2p_allgather_async": (ci, [vp, sz, vp, vp]),
+    "b200_reduce_partial_exchange_async": (ci, [ci, vp, sz, vp, ctypes.c_uint, ctypes.c_uint, vp, vp, vp, vp]),
+    "b200_scan_total_exchange_async": (ci, [vp, vp, sz, vp, vp]),
+    "b200_histogram_fused_allreduce_async": (ci, [vp, vp, vp, sz, vp]),
     "b200_host_alloc": (ci, [ctypes.POINTER(vp), sz]),
     "b200_host_free": (ci, [vp]),
     "b200_tune_hist_cluster": (ci, [ci]),

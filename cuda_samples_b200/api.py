@@ -172,6 +172,62 @@ def scan_total(d_total, d_Src, n, stream=None):
     check(lib.b200_scan_total_async(_dptr(d_total), _dptr(d_Src), n, _stream(stream)), "scan_total")
 
 
+# ------------------------------------------------ fused compute + exchange over NVLink peer windows
+def p2p_window_create():
+    """-> the 64-byte CUDA IPC handle of this rank's exchange window (created on first call)."""
+    buf = ctypes.create_string_buffer(64)
+    check(lib.b200_p2p_window_create(buf), "p2p_window_create")
+    return buf.raw
+
+
+def p2p_connect(rank, world, handles):
+    """handles: list of `world` 64-byte IPC handles in rank order (every rank's p2p_window_create())."""
+    blob = b"".join(handles)
+    assert len(blob) == 64 * world
+    check(lib.b200_p2p_connect(rank, world, blob), "p2p_connect")
+
+
+def p2p_disconnect():
+    check(lib.b200_p2p_disconnect(), "p2p_disconnect")
+
+
+def p2p_world():
+    return int(lib.b200_p2p_world())
+
+
+def p2p_errors():
+    n = ctypes.c_ulonglong(0)
+    check(lib.b200_p2p_errors(ctypes.byref(n)), "p2p_errors")
+    return int(n.value)
+
+
+def p2p_allgather(d_payload, nbytes, d_gathered, stream=None):
+    check(lib.b200_p2p_allgather_async(_dptr(d_payload), nbytes, _dptr(d_gathered), _stream(stream)), "p2p_allgather")
+
+
+def reduce_partial_exchange(d_idata, size, d_slots, index, count, d_gathered, d_sums, d_carry=None, stream=None):
+    """reduce -> exchange in one kernel: fills d_slots[index], then all ranks' slots land in d_gathered
+    ([world][count] doubles) and their rank-order sums in d_sums ([count])."""
+    kind = {"i32": 0, "f32": 1, "f64": 2}.get(_REDUCE.get(str(d_idata.dtype)))
+    if kind is None:
+        raise TypeError("reduce_partial_exchange: unsupported dtype %s" % d_idata.dtype)
+    check(lib.b200_reduce_partial_exchange_async(kind, _dptr(d_idata), size, _dptr(d_slots), index, count,
+                                                 _dptr(d_gathered), _dptr(d_sums), _dptr(d_carry), _stream(stream)),
+          "reduce_partial_exchange")
+
+
+def scan_total_exchange(d_carry, d_Src, n, d_work, stream=None):
+    """Shard total -> peers -> d_carry[0] = wrapping sum of the lower ranks' totals.  d_work: float64[>= 2 + world]."""
+    check(lib.b200_scan_total_exchange_async(_dptr(d_carry), _dptr(d_Src), n, _dptr(d_work), _stream(stream)),
+          "scan_total_exchange")
+
+
+def histogram_fused_allreduce(d_Histogram256, d_Histogram64, d_Data, byteCount, stream=None):
+    """Both histograms of ALL ranks' shards on every rank; the bins are exchanged by the kernel itself."""
+    check(lib.b200_histogram_fused_allreduce_async(_dptr(d_Histogram256), _dptr(d_Histogram64), _dptr(d_Data),
+                                                   byteCount, _stream(stream)), "histogram_fused_allreduce")
+
+
 # ------------------------------------------------------------------------------------ mergeSort
 def initMergeSort():
     lib.initMergeSort()

@@ -21,6 +21,7 @@
 
 #include "common.cuh"
 #include "internal.h"
+#include "p2p.cuh"
 
 namespace cg = cooperative_groups;
 
@@ -29,7 +30,8 @@ namespace b200 {
 constexpr int kHistThreads = 1024;
 constexpr int kHistUnroll  = 8;
 
-enum HistMode { kHist256 = 0, kHist64 = 1, kHistFused = 2 };
+// kHistFusedP2P: the fused mode whose last CTA also all-reduces the 256 bins over the NVLink peer windows (p2p.cuh)
+enum HistMode { kHist256 = 0, kHist64 = 1, kHistFused = 2, kHistFusedP2P = 3 };
 
 // scratch layout (u32 words): [0] ticket, [4..260) acc256, [260..324) acc64
 constexpr int kHistAcc256 = 4;
@@ -60,7 +62,7 @@ template <int BINS, int SH> __device__ __forceinline__ void count_vec(unsigned *
 template <int MODE>
 __global__ void __launch_bounds__(kHistThreads, 1)
     histogram_kernel(const unsigned char *__restrict__ data, size_t n, unsigned *__restrict__ out256,
-                     unsigned *__restrict__ out64, unsigned *__restrict__ scratch)
+                     unsigned *__restrict__ out64, unsigned *__restrict__ scratch, P2PArgs p2p)
 {
     constexpr int BINS = (MODE == kHist64) ? 64 : 256;
     constexpr int SH   = (MODE == kHist64) ? 2 : 0;
@@ -155,7 +157,23 @@ __global__ void __launch_bounds__(kHistThreads, 1)
     if (!s_last)
         return;
     __threadfence();
-    if (threadIdx.x < BINS) {
+    if (MODE == kHistFusedP2P) { // histogram -> all-reduce in the same kernel: bins to every peer, sum of all ranks back
+        __shared__ unsigned long long s_seq;
+        const unsigned               seq = p2p_exchange(p2p, acc, BINS, &s_seq);
+        __syncthreads(); // every thread has read its share of acc before it is re-zeroed below
+        if (threadIdx.x < BINS) {
+            unsigned total = 0;
+            for (unsigned r = 0; r < p2p.world; r++)
+                total += p2p_peer_word(p2p, seq, r, threadIdx.x); // u32 wrap-add: order-independent, bit-exact
+            acc[threadIdx.x]    = 0;
+            out256[threadIdx.x] = total;
+            unsigned s4         = total + __shfl_xor_sync(0xffffffffu, total, 1);
+            s4 += __shfl_xor_sync(0xffffffffu, s4, 2);
+            if ((threadIdx.x & 3) == 0)
+                out64[threadIdx.x >> 2] = s4;
+        }
+    }
+    else if (threadIdx.x < BINS) {
         unsigned total   = __ldcg(&acc[threadIdx.x]);
         acc[threadIdx.x] = 0;
         if (MODE == kHist64) {
@@ -179,7 +197,8 @@ __global__ void __launch_bounds__(kHistThreads, 1)
 static int g_hist_cluster = 2; // CTAs per cluster (1, 2, 4 or 8); 2 packs 148 SMs exactly
 
 template <int MODE>
-static int launch_hist(unsigned *out256, unsigned *out64, const void *d_data, size_t n, cudaStream_t stream)
+static int launch_hist(unsigned *out256, unsigned *out64, const void *d_data, size_t n, cudaStream_t stream,
+                       const P2PArgs *p2p = nullptr)
 {
     int        st = 0;
     DeviceCtx *c  = ctx(&st);
@@ -207,7 +226,7 @@ static int launch_hist(unsigned *out256, unsigned *out64, const void *d_data, si
     cfg.attrs              = at;
     cfg.numAttrs           = 1;
     B200_TRY(cudaLaunchKernelEx(&cfg, histogram_kernel<MODE>, (const unsigned char *)d_data, n, out256, out64,
-                                (unsigned *)c->hist.ptr));
+                                (unsigned *)c->hist.ptr, p2p ? *p2p : P2PArgs()));
     count_launch();
     return 0;
 }
@@ -240,3 +259,13 @@ extern "C" int b200_histogram_fused_async(uint32_t *d_hist256, uint32_t *d_hist6
 }
 // tuning knob used by bench.py / tests (not part of the stable ABI)
 extern "C" int b200_tune_hist_cluster(int cluster) { return set_hist_cluster(cluster); }
+// Both histograms of the concatenation of ALL ranks' shards, on every rank, in one kernel per rank: the last CTA
+// stores its 256 bins into every peer's window over NVLink and sums the G payloads (b200_p2p_connect first).
+extern "C" int b200_histogram_fused_allreduce_async(uint32_t *d_hist256, uint32_t *d_hist64, const void *d_data,
+                                                    size_t byteCount, b200_stream_t stream)
+{
+    const P2PArgs *a = p2p_args();
+    if (!a || a->world == 0)
+        return (int)cudaErrorInvalidValue;
+    return launch_hist<kHistFusedP2P>(d_hist256, d_hist64, d_data, byteCount, (cudaStream_t)stream, a);
+}

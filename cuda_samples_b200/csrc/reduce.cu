@@ -15,6 +15,7 @@
 // Roofline: HBM-bound, sizeof(T) algorithmic bytes per element (read once, nothing written).
 #include "common.cuh"
 #include "internal.h"
+#include "p2p.cuh"
 
 namespace b200 {
 
@@ -117,12 +118,26 @@ template <typename Part> __device__ __forceinline__ Part block_sum(Part v, Part 
     return r; // valid in warp 0
 }
 
+// What the last CTA does after the local sum when the kernel also carries the node-wide exchange (kP2P):
+// d_slots[0..count) are this rank's shard partials (doubles; this launch fills [index], earlier launches on the
+// stream the others); they are stored into every peer's window, every rank's slots are gathered, and
+// sums[k] = sum over ranks (rank order, fp64) of slot k.  carry (optional) = sum of slot [index] over the LOWER
+// ranks as wrapping u32: the carry-in of this rank's shard in a sharded scan.
+struct ReduceExchange {
+    P2PArgs   p2p;
+    double   *slots;
+    double   *gathered; // [world][count]
+    double   *sums;     // [count]
+    unsigned *carry;    // nullable
+    unsigned  index, count;
+};
+
 // scratch layout: [0] ticket (u32), [16 ..) one 8-byte partial per CTA
-template <typename L>
+template <typename L, bool kP2P>
 __global__ void __launch_bounds__(kReduceThreads, kReduceCtasPerSm)
     reduce_kernel(const typename L::Elem *__restrict__ in, size_t n, typename L::Elem *__restrict__ out,
                   size_t out_len, unsigned *__restrict__ ticket, typename L::Part *__restrict__ partials,
-                  double *__restrict__ out_f64)
+                  double *__restrict__ out_f64, ReduceExchange ex)
 {
     typedef typename L::Elem Elem;
     typedef typename L::Part Part;
@@ -192,11 +207,36 @@ __global__ void __launch_bounds__(kReduceThreads, kReduceCtasPerSm)
     }
     for (size_t i = 1 + threadIdx.x; i < out_len; i += kReduceThreads)
         out[i] = Elem(0);
+    if (kP2P) { // compute -> collective in the same kernel: P2P stores over NVLink, no NCCL call
+        __shared__ unsigned long long s_seq;
+        __syncthreads(); // slot [index] (written by thread 0 just above) is visible to the CTA
+        const unsigned           words = 2 * ex.count;
+        const unsigned seq =
+            p2p_exchange(ex.p2p, reinterpret_cast<const unsigned *>(ex.slots), words, &s_seq);
+        auto peer = [&](unsigned r, unsigned k) {
+            return __hiloint2double((int)p2p_peer_word(ex.p2p, seq, r, 2 * k + 1),
+                                    (int)p2p_peer_word(ex.p2p, seq, r, 2 * k));
+        };
+        for (unsigned i = threadIdx.x; i < ex.p2p.world * ex.count; i += kReduceThreads)
+            ex.gathered[i] = peer(i / ex.count, i % ex.count);
+        if (threadIdx.x < ex.count) {
+            double t = 0.0;
+            for (unsigned r = 0; r < ex.p2p.world; r++)
+                t += peer(r, threadIdx.x);
+            ex.sums[threadIdx.x] = t;
+        }
+        if (ex.carry && threadIdx.x == 0) {
+            unsigned cin = 0;
+            for (unsigned r = 0; r < ex.p2p.rank; r++)
+                cin += (unsigned)(long long)peer(r, ex.index);
+            *ex.carry = cin;
+        }
+    }
 }
 
 template <typename L>
 static int launch_reduce(const typename L::Elem *d_in, size_t n, typename L::Elem *d_out, size_t out_len,
-                         cudaStream_t stream, double *d_out_f64 = nullptr)
+                         cudaStream_t stream, double *d_out_f64 = nullptr, const ReduceExchange *ex = nullptr)
 {
     int        st = 0;
     DeviceCtx *c  = ctx(&st);
@@ -212,7 +252,12 @@ static int launch_reduce(const typename L::Elem *d_in, size_t n, typename L::Ele
         grid = 1;
     unsigned *ticket   = reinterpret_cast<unsigned *>(c->reduce.ptr);
     auto     *partials = reinterpret_cast<typename L::Part *>(reinterpret_cast<char *>(c->reduce.ptr) + 16);
-    reduce_kernel<L><<<grid, kReduceThreads, 0, stream>>>(d_in, n, d_out, out_len, ticket, partials, d_out_f64);
+    if (ex)
+        reduce_kernel<L, true><<<grid, kReduceThreads, 0, stream>>>(d_in, n, d_out, out_len, ticket, partials,
+                                                                   d_out_f64, *ex);
+    else
+        reduce_kernel<L, false><<<grid, kReduceThreads, 0, stream>>>(d_in, n, d_out, out_len, ticket, partials,
+                                                                    d_out_f64, ReduceExchange());
     count_launch();
     B200_TRY(cudaGetLastError());
     return 0;
@@ -247,4 +292,41 @@ extern "C" int b200_reduce_partial_async(int kind, const void *d_in, size_t n, d
     case 2: return launch_reduce<LaneF64>((const double *)d_in, n, nullptr, 0, (cudaStream_t)stream, d_slot);
     }
     return (int)cudaErrorInvalidValue;
+}
+
+// The same, fused with the node-wide exchange over the NVLink peer windows (p2p.cuh; b200_p2p_connect first).
+// d_slots[0..count): this rank's shard partials, slot [index] is produced by this launch.  On return (stream
+// order) d_gathered[r * count + k] = rank r's slot k, d_sums[k] = their sum in rank order (fp64), and, when
+// d_carry is not null, *d_carry = wrapping u32 sum of slot [index] over the ranks below this one.
+extern "C" int b200_reduce_partial_exchange_async(int kind, const void *d_in, size_t n, double *d_slots,
+                                                  unsigned index, unsigned count, double *d_gathered, double *d_sums,
+                                                  uint32_t *d_carry, b200_stream_t stream)
+{
+    const P2PArgs *a = p2p_args();
+    if (!a || a->world == 0 || count == 0 || index >= count || 8u * count > kP2PSlotBytes ||
+        count > (unsigned)kReduceThreads)
+        return (int)cudaErrorInvalidValue;
+    ReduceExchange ex;
+    ex.p2p      = *a;
+    ex.slots    = d_slots;
+    ex.gathered = d_gathered;
+    ex.sums     = d_sums;
+    ex.carry    = d_carry;
+    ex.index    = index;
+    ex.count    = count;
+    double *slot = d_slots + index;
+    switch (kind) {
+    case 0: return launch_reduce<LaneI32>((const int *)d_in, n, nullptr, 0, (cudaStream_t)stream, slot, &ex);
+    case 1: return launch_reduce<LaneF32>((const float *)d_in, n, nullptr, 0, (cudaStream_t)stream, slot, &ex);
+    case 2: return launch_reduce<LaneF64>((const double *)d_in, n, nullptr, 0, (cudaStream_t)stream, slot, &ex);
+    }
+    return (int)cudaErrorInvalidValue;
+}
+
+// Sharded long scan, step 1 fused with its exchange: shard total -> every peer -> *d_carry = wrapping sum of the
+// lower ranks' totals (the d_carry argument of b200_scan_exclusive_async).  d_work: >= 2 + world doubles.
+extern "C" int b200_scan_total_exchange_async(uint32_t *d_carry, const uint32_t *d_src, size_t n, double *d_work,
+                                              b200_stream_t stream)
+{
+    return b200_reduce_partial_exchange_async(0, d_src, n, d_work, 0, 1, d_work + 2, d_work + 1, d_carry, stream);
 }

@@ -14,6 +14,11 @@ Only the exchange step each primitive really has is a collective:
                                          out in source-rank order, local stable sort.  Stable globally:
                                          equal keys share a bucket, sources arrive in rank (= index) order.
 
+With enable_p2p() (CUDA only, one NVSwitch node) the three small exchanges -- bins, shard sums, shard totals --
+leave NCCL altogether: the last CTA of the producing kernel stores its payload into every peer's window over
+NVLink, waits for the peers' flags and finishes the combine (csrc/p2p.cuh).  NCCL then only carries the control
+plane (IPC handles, barriers) and the sort's all-to-all.
+
 The local compute is an injected `ops` object: `CudaOps` (libb200prim.so, the product path) by default.
 The CPU test-suite (gloo, world_size 2) injects a numpy stand-in that lives in tests/ -- there is no
 CPU path in this package.
@@ -24,10 +29,53 @@ import torch.distributed as dist
 from . import api
 
 
+_P2P = {"world": 0}
+
+
+def enable_p2p(group=None):
+    """Create this rank's exchange window, swap the CUDA IPC handles over the process group and map the peers.
+    Collective: every rank of `group` must call it.  -> True when the fused kernels will be used."""
+    rank, world = _world(group)
+    if world == 1 or world > 16:
+        return False
+    handles = [None] * world
+    dist.all_gather_object(handles, api.p2p_window_create(), group=group)
+    api.p2p_connect(rank, world, handles)
+    dist.barrier(group=group)
+    _P2P["world"] = world
+    return True
+
+
+def disable_p2p(group=None):
+    if _P2P["world"]:
+        torch.cuda.synchronize()
+        dist.barrier(group=group)
+        api.p2p_disconnect()
+        _P2P["world"] = 0
+
+
+def p2p_enabled():
+    return _P2P["world"] > 1
+
+
 class CudaOps:
     """Local steps on the current CUDA device through the C ABI."""
 
     device_type = "cuda"
+
+    def histogram_fused_allreduce(self, data, nbytes):
+        bins = torch.empty(320, dtype=torch.int32, device=data.device)
+        api.histogram_fused_allreduce(bins[:256], bins[256:], data, nbytes)
+        return bins
+
+    def reduce_partial_exchange(self, x, n, slots, index, count, gathered, sums):
+        api.reduce_partial_exchange(x, n, slots, index, count, gathered, sums)
+
+    def scan_total_exchange(self, src, n):
+        carry = torch.empty(1, dtype=torch.int32, device=src.device)
+        work = torch.empty(2 + 16, dtype=torch.float64, device=src.device)
+        api.scan_total_exchange(carry, src, n, work)
+        return carry
 
     def histogram_fused(self, data, nbytes):
         bins = torch.empty(320, dtype=torch.int32, device=data.device)
@@ -77,6 +125,9 @@ def _u32_as_i64(t):
 def histogram_sharded(data, nbytes, ops=None, group=None):
     """-> (hist256, hist64) of the concatenation of all ranks' shards, on every rank (int32 = u32 bits)."""
     ops = ops or CudaOps()
+    if p2p_enabled() and isinstance(ops, CudaOps) and _world(group)[1] == _P2P["world"]:
+        bins = ops.histogram_fused_allreduce(data, nbytes)  # one kernel: histogram + exchange over NVLink
+        return bins[:256], bins[256:]
     bins = ops.histogram_fused(data, nbytes)
     if _world(group)[1] > 1:
         dist.all_reduce(bins, op=dist.ReduceOp.SUM, group=group)
@@ -139,9 +190,19 @@ def reduce_many_sharded(tensors, ns, ops=None, group=None, overlap=False):
     rank, world = _world(group)
     k = len(tensors)
     buf = torch.empty(k, dtype=torch.float64, device=tensors[0].device)
+    dtypes = [x.dtype for x in tensors]
+    if p2p_enabled() and isinstance(ops, CudaOps) and world == _P2P["world"]:
+        # the last local kernel also carries the exchange and the rank-order sums: no collective call at all
+        gathered = torch.empty(world * k, dtype=torch.float64, device=buf.device)
+        sums = torch.empty(k, dtype=torch.float64, device=buf.device)
+        for i, (x, n) in enumerate(zip(tensors, ns)):
+            if i < k - 1:
+                ops.reduce_partial(x, n, buf[i:i + 1])
+            else:
+                ops.reduce_partial_exchange(x, n, buf, i, k, gathered, sums)
+        return PendingReduce(None, sums, 1, dtypes)
     for i, (x, n) in enumerate(zip(tensors, ns)):
         ops.reduce_partial(x, n, buf[i:i + 1])
-    dtypes = [x.dtype for x in tensors]
     if world == 1:
         return PendingReduce(None, buf, 1, dtypes)
     gathered = torch.empty(world * k, dtype=torch.float64, device=buf.device)
@@ -165,6 +226,9 @@ def scan_sharded(dst, src, n_local, ops=None, group=None):
     rank, world = _world(group)
     if world == 1:
         ops.scan_with_carry(dst, src, n_local, None)
+        return dst
+    if p2p_enabled() and isinstance(ops, CudaOps) and world == _P2P["world"]:
+        ops.scan_with_carry(dst, src, n_local, ops.scan_total_exchange(src, n_local))  # 2 kernels, no collective call
         return dst
     total = ops.scan_total(src, n_local)
     totals = torch.empty(world, dtype=torch.int32, device=total.device)

@@ -99,6 +99,35 @@ int b200_segmented_sort_kv_async(uint32_t *d_dstKey, uint32_t *d_dstVal, const u
 int b200_generate_async(void *d_out, size_t first, size_t n, uint64_t seed, int kind, uint32_t param,
                         b200_stream_t stream);
 
+/* ---- fused compute + collective over NVLink peer windows (one process per GPU, one NVSwitch node) -------------
+ * The reference has no multi-GPU path for these primitives; the sharded versions end in a tiny
+ * exchange (320 bins / a few shard sums / G shard totals).  Instead of a separate NCCL collective the last CTA of
+ * the producing kernel stores its payload into every peer's window (P2P stores), flags it, waits for the peers'
+ * flags and finishes the combine itself.  Setup: every rank calls b200_p2p_window_create (64-byte CUDA IPC
+ * handle out), the handles are exchanged by the caller's control plane (multi_gpu.py: torch.distributed), then
+ * b200_p2p_connect(rank, world, handles[world][64]).  Every rank must issue the same sequence of exchange calls,
+ * stream-ordered.  A peer that never arrives is reported by b200_p2p_errors (bounded wait), not by a hang. */
+int b200_p2p_window_create(unsigned char *handle_out /* 64 bytes */);
+int b200_p2p_connect(int rank, int world, const unsigned char *handles);
+int b200_p2p_disconnect(void);
+int b200_p2p_world(void); /* 0 until connected */
+int b200_p2p_errors(unsigned long long *count);
+/* d_gathered[r * nbytes ..) = rank r's payload on every rank; nbytes % 4 == 0, <= 2048 */
+int b200_p2p_allgather_async(const void *d_payload, size_t nbytes, void *d_gathered, b200_stream_t stream);
+/* reduce -> exchange: d_slots[0..count) are this rank's shard partials (b200_reduce_partial_async fills the
+ * others, this launch fills [index]); on every rank d_gathered[r*count + k] = rank r's slot k and
+ * d_sums[k] = sum over ranks in rank order (fp64, deterministic).  d_carry (nullable) = wrapping u32 sum of slot
+ * [index] over the LOWER ranks (the carry-in of this shard in a sharded scan). */
+int b200_reduce_partial_exchange_async(int kind, const void *d_in, size_t n, double *d_slots, unsigned index,
+                                       unsigned count, double *d_gathered, double *d_sums, uint32_t *d_carry,
+                                       b200_stream_t stream);
+/* sharded long scan, step 1: shard total -> peers -> *d_carry; d_work: >= 2 + world doubles of scratch */
+int b200_scan_total_exchange_async(uint32_t *d_carry, const uint32_t *d_src, size_t n, double *d_work,
+                                   b200_stream_t stream);
+/* histogram64 + histogram256 of the concatenation of all ranks' shards, on every rank, one kernel per rank */
+int b200_histogram_fused_allreduce_async(uint32_t *d_hist256, uint32_t *d_hist64, const void *d_data,
+                                         size_t byteCount, b200_stream_t stream);
+
 /* host-buffer variants: H2D copies, kernels and D2H of the result are all inside the call
  * (chunked and double-buffered so the copy engine and the SMs overlap); they synchronise before
  * returning.  These are what bench.py's `e2e` number times. */

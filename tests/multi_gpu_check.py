@@ -28,35 +28,69 @@ def main():
         if not ok:
             failures.append(name)
 
-    # histogram: 16 MiB per rank
-    n = 16 << 20
-    d = torch.empty(n, dtype=torch.uint8, device="cuda")
-    prim.generate(d, "bytes", rank * n, n, 2009)
-    h256, h64 = mg.histogram_sharded(d, n)
-    whole = oracle.generate("bytes", 0, world * n, 2009)
-    check("hist256", (h256.cpu().numpy().view(np.uint32) == oracle.histogram256(whole)).all())
-    check("hist64", (h64.cpu().numpy().view(np.uint32) == oracle.histogram64(whole)).all())
+    def small_exchanges(tag):
+        # histogram: 16 MiB per rank
+        n = 16 << 20
+        d = torch.empty(n, dtype=torch.uint8, device="cuda")
+        prim.generate(d, "bytes", rank * n, n, 2009)
+        h256, h64 = mg.histogram_sharded(d, n)
+        whole = oracle.generate("bytes", 0, world * n, 2009)
+        check(tag + "hist256", (h256.cpu().numpy().view(np.uint32) == oracle.histogram256(whole)).all())
+        check(tag + "hist64", (h64.cpu().numpy().view(np.uint32) == oracle.histogram64(whole)).all())
 
-    # reduce: 2^24 per rank
-    n = 1 << 24
-    xi = torch.empty(n, dtype=torch.int32, device="cuda")
-    xf = torch.empty(n, dtype=torch.float32, device="cuda")
-    prim.generate(xi, "i32_byte", rank * n, n, 1)
-    prim.generate(xf, "f32_byte", rank * n, n, 1)
-    gi, gf = mg.reduce_sharded(xi, n), mg.reduce_sharded(xf, n)
-    check("reduce_int", int(gi.item()) == oracle.reduce(oracle.generate("i32_byte", 0, world * n, 1)))
-    want = oracle.reduce(oracle.generate("f32_byte", 0, world * n, 1))
-    check("reduce_float", abs(float(gf.item()) - want) <= 1e-5 * abs(want))
-    ti, tf = mg.reduce_many_sharded([xi, xf], [n, n]).typed()
-    check("reduce_many", ti == int(gi.item()) and abs(tf - want) <= 1e-5 * abs(want))
+        # reduce: 2^24 per rank
+        n = 1 << 24
+        xi = torch.empty(n, dtype=torch.int32, device="cuda")
+        xf = torch.empty(n, dtype=torch.float32, device="cuda")
+        prim.generate(xi, "i32_byte", rank * n, n, 1)
+        prim.generate(xf, "f32_byte", rank * n, n, 1)
+        gi, gf = mg.reduce_sharded(xi, n), mg.reduce_sharded(xf, n)
+        check(tag + "reduce_int", int(gi.item()) == oracle.reduce(oracle.generate("i32_byte", 0, world * n, 1)))
+        want = oracle.reduce(oracle.generate("f32_byte", 0, world * n, 1))
+        check(tag + "reduce_float", abs(float(gf.item()) - want) <= 1e-5 * abs(want))
+        ti, tf = mg.reduce_many_sharded([xi, xf], [n, n]).typed()
+        check(tag + "reduce_many", ti == int(gi.item()) and abs(tf - want) <= 1e-5 * abs(want))
 
-    # scan: one array of world * 2^24 elements, contiguous shards
-    src = torch.empty(n, dtype=torch.int32, device="cuda")
-    prim.generate(src, "u31", rank * n, n, 2009)
-    dst = torch.empty_like(src)
-    mg.scan_sharded(dst, src, n)
-    want = oracle.scan_exclusive(oracle.generate("u31", 0, world * n, 2009), 1, world * n)[rank * n:(rank + 1) * n]
-    check("scan", (dst.cpu().numpy().view(np.uint32) == want).all())
+        # scan: one array of world * 2^24 elements, contiguous shards
+        src = torch.empty(n, dtype=torch.int32, device="cuda")
+        prim.generate(src, "u31", rank * n, n, 2009)
+        dst = torch.empty_like(src)
+        mg.scan_sharded(dst, src, n)
+        want = oracle.scan_exclusive(oracle.generate("u31", 0, world * n, 2009), 1, world * n)[rank * n:(rank + 1) * n]
+        check(tag + "scan", (dst.cpu().numpy().view(np.uint32) == want).all())
+
+    small_exchanges("nccl:")
+    # the same three paths with the exchange fused into the producing kernel (NVLink peer windows, csrc/p2p.cuh)
+    check("enable_p2p", mg.enable_p2p())
+    pay = torch.arange(rank * 100, rank * 100 + 24, dtype=torch.int32, device="cuda")
+    got = torch.empty(world * 24, dtype=torch.int32, device="cuda")
+    for _ in range(5):  # repeated exchanges exercise both slot parities
+        prim.p2p_allgather(pay, 96, got)
+    want_all = torch.cat([torch.arange(r * 100, r * 100 + 24, dtype=torch.int32) for r in range(world)])
+    check("p2p_allgather", bool((got.cpu() == want_all).all()))
+    for _ in range(3):
+        small_exchanges("p2p:")
+    torch.cuda.synchronize()
+    check("p2p_errors", prim.p2p_errors() == 0)
+    # latency of the exchange alone: NCCL all_gather vs the peer-window kernel (CUDA events, 200 calls each)
+    small = torch.zeros(2, dtype=torch.float64, device="cuda")
+    out = torch.empty(2 * world, dtype=torch.float64, device="cuda")
+    for name, fn in (("nccl all_gather_into_tensor", lambda: dist.all_gather_into_tensor(out, small)),
+                     ("p2p_allgather kernel", lambda: prim.p2p_allgather(small, 16, out))):
+        for _ in range(20):
+            fn()
+        torch.cuda.synchronize()
+        dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(200):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        if rank == 0:
+            print("exchange of 16 B per rank, world=%d: %-28s %.2f us per call" % (world, name, e0.elapsed_time(e1) * 5),
+                  flush=True)
+    mg.disable_p2p()
 
     # sort: world * 2^22 pairs, three datasets, both directions
     n = 1 << 22
