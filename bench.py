@@ -183,7 +183,7 @@ def run_reference(args):
 
 
 # ---------------------------------------------------------------------------------- primitives table
-def primitives_table(torch, dist, prim, mg, rank, world, peak, barrier):
+def primitives_table(torch, dist, prim, mg, rank, world, peak, barrier, p2p=False):
     """GB/s (Gkeys/s for sort) of every primitive of the path, device-resident inputs, CUDA events."""
     table = {}
 
@@ -225,7 +225,8 @@ def primitives_table(torch, dist, prim, mg, rank, world, peak, barrier):
     def step_fused():
         mg.histogram_sharded(d, big)
     record("histogram64+256_fused_4GiB_per_gpu", time_steps(torch, step_fused, 5, 2, barrier) / 5, big * world,
-           {"scaling": "weak", "collective": "all_reduce(320 x u32)" if world > 1 else None,
+           {"scaling": "weak", "collective": (("in-kernel NVLink peer-window all-reduce (256 x u32)" if p2p else
+                                              "all_reduce(320 x u32)") if world > 1 else None),
             "note": "1 B per input byte for BOTH histograms (one pass)"})
     h256b = torch.empty(256, dtype=torch.int32, device="cuda")
 
@@ -242,7 +243,8 @@ def primitives_table(torch, dist, prim, mg, rank, world, peak, barrier):
     def step_scan():
         mg.scan_sharded(dst, src, n)
     record("scanExclusiveLarge_2^28", time_steps(torch, step_scan, 20, 4, barrier) / 20, 8 * N_ELEMS,
-           {"scaling": "strong", "collective": "all_gather(G x u32)" if world > 1 else None})
+           {"scaling": "strong", "collective": (("in-kernel NVLink peer-window exchange of shard totals" if p2p else
+                                                "all_gather(G x u32)") if world > 1 else None)})
     if world == 1:
         def step_scan_short():
             prim.scanExclusiveShort(dst, src, n // 1024, 1024)
@@ -302,6 +304,9 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     barrier = (lambda: dist.barrier()) if world > 1 else None
+    # N > 1: the small exchanges are done by the producing kernels themselves over NVLink peer windows
+    # (csrc/p2p.cuh); B200_BENCH_P2P=0 falls back to one NCCL collective per step for comparison
+    p2p = world > 1 and os.environ.get("B200_BENCH_P2P", "1") == "1" and mg.enable_p2p()
     peak, peak_src = measured_peak()
 
     # ---- inputs, resident in HBM (each rank generates its own slice of the global stream)
@@ -333,9 +338,9 @@ def run_ours(args):
     seconds = time_steps(torch, step, args.steps, args.warmup, barrier, finish)
     launches = prim.launch_count() - launches0 - 2 * args.warmup
     seconds = max_over_ranks(torch, dist, seconds, world)
-    # keep the same load running ~1.5 s so the 100 ms clock poller sees it (untimed)
-    t_end = time.perf_counter() + 1.5
-    while time.perf_counter() < t_end:
+    # keep the same load running ~1.5 s so the 100 ms clock poller sees it (untimed); the iteration count is
+    # derived from the max-over-ranks time so that every rank issues the same number of exchanges
+    for _ in range(max(1, int(1.5 / (seconds / args.steps) / 50))):
         for _ in range(50):
             step()
         finish()
@@ -371,10 +376,12 @@ def run_ours(args):
         del xi, xf
         torch.cuda.empty_cache()
         try:
-            table = primitives_table(torch, dist, prim, mg, rank, world, peak, barrier)
+            table = primitives_table(torch, dist, prim, mg, rank, world, peak, barrier, p2p)
         except Exception as e:  # the headline must still be printed
             table = {"error": repr(e)}
 
+    if p2p:
+        mg.disable_p2p()
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -405,6 +412,10 @@ def run_ours(args):
         pass
     cfg = base_config(world)
     cfg["clock_probe"] = "same step looped ~1.5 s after the timed region for the 100 ms nvidia-smi poller"
+    if world > 1:
+        cfg["exchange"] = ("fused into the last reduce kernel of the step: P2P stores into NVLink peer windows + "
+                           "rank-order fp64 sum (csrc/p2p.cuh), no NCCL call in the timed region") if p2p else \
+            "one NCCL all_gather of the two shard partials per step"
     line = {"metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": seconds / args.steps * 1e3, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "i32+f32", "data": "synthetic", "config": cfg,
