@@ -52,6 +52,12 @@ SIGNATURES = {
     "b200_reduce_partial_exchange_async": (ci, [ci, vp, sz, vp, ctypes.c_uint, ctypes.c_uint, vp, vp, vp, vp]),
     "b200_scan_total_exchange_async": (ci, [vp, vp, sz, vp, vp]),
     "b200_histogram_fused_allreduce_async": (ci, [vp, vp, vp, sz, vp]),
+    "b200_p2p_buffer_create": (ci, [sz, ctypes.POINTER(vp), ctypes.c_char_p]),
+    "b200_p2p_buffer_open": (ci, [ctypes.c_char_p, ctypes.POINTER(vp)]),
+    "b200_p2p_buffer_close": (ci, [vp]),
+    "b200_p2p_buffer_free": (ci, [vp]),
+    "b200_partition_exchange_kv_async": (ci, [vp, vp, sz, vp, u32, ctypes.POINTER(vp), ctypes.POINTER(vp), sz, vp, vp,
+                                              vp]),
     "b200_host_alloc": (ci, [ctypes.POINTER(vp), sz]),
     "b200_host_free": (ci, [vp]),
     "b200_tune_hist_cluster": (ci, [ci]),

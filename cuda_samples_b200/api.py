@@ -205,6 +205,39 @@ def p2p_allgather(d_payload, nbytes, d_gathered, stream=None):
     check(lib.b200_p2p_allgather_async(_dptr(d_payload), nbytes, _dptr(d_gathered), _stream(stream)), "p2p_allgather")
 
 
+def p2p_buffer_create(nbytes):
+    """-> (device pointer as int, 64-byte IPC handle) of a cudaMalloc'ed buffer other ranks can map."""
+    ptr, buf = ctypes.c_void_p(0), ctypes.create_string_buffer(64)
+    check(lib.b200_p2p_buffer_create(nbytes, ctypes.byref(ptr), buf), "p2p_buffer_create")
+    return int(ptr.value), buf.raw
+
+
+def p2p_buffer_open(handle):
+    ptr = ctypes.c_void_p(0)
+    check(lib.b200_p2p_buffer_open(handle, ctypes.byref(ptr)), "p2p_buffer_open")
+    return int(ptr.value)
+
+
+def p2p_buffer_close(ptr):
+    check(lib.b200_p2p_buffer_close(ctypes.c_void_p(ptr)), "p2p_buffer_close")
+
+
+def p2p_buffer_free(ptr):
+    check(lib.b200_p2p_buffer_free(ctypes.c_void_p(ptr)), "p2p_buffer_free")
+
+
+def partition_exchange_kv(srcKey, srcVal, N, d_splitters, sortDir, recv_keys, recv_vals, capacity, d_matrix, d_info,
+                          stream=None):
+    """Stable partition by splitters whose bucket runs are stored straight into the destination ranks' receive
+    buffers (recv_keys / recv_vals: lists of `world` int device pointers).  See include/b200prim.h."""
+    w = len(recv_keys)
+    ka = (ctypes.c_void_p * w)(*recv_keys)
+    va = (ctypes.c_void_p * w)(*recv_vals)
+    check(lib.b200_partition_exchange_kv_async(_dptr(srcKey), _dptr(srcVal), N, _dptr(d_splitters), sortDir, ka, va,
+                                               capacity, _dptr(d_matrix), _dptr(d_info), _stream(stream)),
+          "partition_exchange_kv")
+
+
 def reduce_partial_exchange(d_idata, size, d_slots, index, count, d_gathered, d_sums, d_carry=None, stream=None):
     """reduce -> exchange in one kernel: fills d_slots[index], then all ranks' slots land in d_gathered
     ([world][count] doubles) and their rank-order sums in d_sums ([count])."""

@@ -144,3 +144,30 @@ extern "C" int b200_p2p_allgather_async(const void *d_payload, size_t nbytes, vo
     B200_TRY(cudaGetLastError());
     return 0;
 }
+
+// ---- large peer-mapped buffers (the receive buffers of the fused partition + exchange) --------------------------
+extern "C" int b200_p2p_buffer_create(size_t bytes, void **d_ptr, unsigned char *handle_out /* 64 bytes */)
+{
+    B200_TRY(cudaMalloc(d_ptr, bytes ? bytes : 16));
+    cudaIpcMemHandle_t h;
+    B200_TRY(cudaIpcGetMemHandle(&h, *d_ptr));
+    memcpy(handle_out, &h, 64);
+    return 0;
+}
+extern "C" int b200_p2p_buffer_open(const unsigned char *handle, void **d_peer)
+{
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, 64);
+    B200_TRY(cudaIpcOpenMemHandle(d_peer, h, cudaIpcMemLazyEnablePeerAccess));
+    return 0;
+}
+extern "C" int b200_p2p_buffer_close(void *d_peer)
+{
+    B200_TRY(cudaIpcCloseMemHandle(d_peer));
+    return 0;
+}
+extern "C" int b200_p2p_buffer_free(void *d_ptr)
+{
+    B200_TRY(cudaFree(d_ptr));
+    return 0;
+}

@@ -21,6 +21,7 @@
 // Traffic model: (4 + 16*4) = 68 B per pair; HBM-bound in bytes, issue-bound in practice.
 #include "common.cuh"
 #include "internal.h"
+#include "p2p.cuh"
 
 namespace b200 {
 
@@ -70,7 +71,21 @@ struct SortSmem {
     unsigned wsum[kRadix / 32];
     unsigned splitters[kRadix];
     unsigned tile;
+    unsigned token;                 // peer variant: payload of the "all my stores are out" exchange
+    unsigned long long p2p_seq;
 };
+
+// Peer variant of the partition (multi-GPU sample sort): bucket b IS rank b, and its run is stored straight into
+// rank b's receive buffer over NVLink instead of into a local array that an all-to-all would copy again.
+struct SortPeer {
+    unsigned long long k[kP2PMaxRanks], v[kP2PMaxRanks]; // receive buffers of every rank (peer-mapped)
+    P2PArgs            p2p;
+    unsigned          *done;   // CTAs of this launch whose stores are fenced
+    const unsigned    *info;   // [0] n_out, [1] != 0: a receive buffer would overflow -> nothing is sent
+};
+struct NoPeer {};
+template <bool kPeer> struct PeerParam { typedef NoPeer type; };
+template <> struct PeerParam<true> { typedef SortPeer type; };
 
 // "digit" of a key: radix byte of (key ^ flip), or the bucket index among ascending splitters
 template <bool kBucket> struct DigitOp {
@@ -163,11 +178,22 @@ __device__ __forceinline__ void finish_digit_offsets(unsigned *ghist, int passes
 // Digit histograms of all passes in one read of the keys; the last CTA turns each 256-bin histogram
 // into exclusive offsets in place.  ghist: [passes][256], zero on entry.
 // ---------------------------------------------------------------------------------------------------
-template <bool kBucket>
+// What the last CTA of the bucket histogram does in the peer variant: the G bucket counts go to every rank, the
+// G x G matrix comes back, and ghist[b] becomes the position of this rank's run inside rank b's receive buffer.
+struct HistPeer {
+    P2PArgs   p2p;
+    unsigned *matrix;   // [world][world] out: matrix[r][b] = pairs rank r sends to rank b
+    unsigned *info;     // [0] pairs this rank receives, [1] overflow flag
+    unsigned  capacity; // pairs a receive buffer can hold
+};
+template <bool kPeer> struct HistPeerParam { typedef NoPeer type; };
+template <> struct HistPeerParam<true> { typedef HistPeer type; };
+
+template <bool kBucket, bool kPeer = false>
 __global__ void __launch_bounds__(kSortThreads)
     sort_hist_kernel(const unsigned *__restrict__ keys, size_t n, unsigned flip, const unsigned *__restrict__ splitters,
                      unsigned nspl, unsigned *__restrict__ ghist, unsigned *__restrict__ ticket,
-                     unsigned *__restrict__ counts_out)
+                     unsigned *__restrict__ counts_out, typename HistPeerParam<kPeer>::type peer)
 {
     constexpr int       P = kBucket ? 1 : 4;
     __shared__ unsigned h[P][kRadix];
@@ -232,6 +258,38 @@ __global__ void __launch_bounds__(kSortThreads)
     finish_digit_offsets(ghist, P, kBucket ? counts_out : nullptr, nspl);
     if (threadIdx.x == 0)
         *ticket = 0;
+    if constexpr (kPeer) {
+        __shared__ unsigned long long s_seq;
+        __shared__ unsigned           s_mat[kP2PMaxRanks * kP2PMaxRanks];
+        __shared__ unsigned           s_over;
+        const unsigned                world = peer.p2p.world, rank = peer.p2p.rank;
+        if (threadIdx.x == 0)
+            s_over = 0;
+        __syncthreads(); // counts_out (written by warp 0 above) is visible to the CTA
+        const unsigned seq = p2p_exchange(peer.p2p, counts_out, world, &s_seq);
+        if (threadIdx.x < world * world) {
+            const unsigned m = p2p_peer_word(peer.p2p, seq, threadIdx.x / world, threadIdx.x % world);
+            s_mat[threadIdx.x]       = m;
+            peer.matrix[threadIdx.x] = m;
+        }
+        __syncthreads();
+        if (threadIdx.x < world) {
+            unsigned off = 0, col = 0;
+            for (unsigned r = 0; r < world; r++) {
+                const unsigned m = s_mat[r * world + threadIdx.x];
+                off += (r < rank) ? m : 0u;
+                col += m;
+            }
+            ghist[threadIdx.x] = off; // sources land in rank order = original index order (global stability)
+            if (col > peer.capacity)
+                atomicOr(&s_over, 1u);
+            if (threadIdx.x == rank)
+                peer.info[0] = col;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0)
+            peer.info[1] = s_over;
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -336,17 +394,45 @@ __global__ void __launch_bounds__(kHist4Threads, 1)
 //   * keys go to shared memory as soon as the bases are known; the values are loaded only then (their latency
 //     hides behind the look-back), so that at most 32 payload registers are live and nothing spills.
 // ---------------------------------------------------------------------------------------------------
-template <bool kBucket, int kLB>
+// All stores of this CTA are fenced; the last CTA of the launch tells every peer and waits for every peer's word:
+// when the kernel ends on a rank, that rank's receive buffer is complete.
+__device__ __forceinline__ void peer_finish(SortSmem &S, const SortPeer &peer)
+{
+    __shared__ bool s_last;
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0)
+        s_last = atomicAdd(peer.done, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!s_last)
+        return;
+    __threadfence_system();
+    if (threadIdx.x == 0)
+        S.token = 1;
+    __syncthreads();
+    const unsigned seq = p2p_exchange(peer.p2p, &S.token, 1, &S.p2p_seq);
+    if (threadIdx.x < peer.p2p.world)
+        (void)p2p_peer_word(peer.p2p, seq, threadIdx.x, 0);
+    __threadfence_system();
+}
+
+template <bool kBucket, int kLB, bool kPeer = false>
 __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
     sort_pass_kernel(const unsigned *__restrict__ kin, const unsigned *__restrict__ vin, unsigned *__restrict__ kout,
                      unsigned *__restrict__ vout, unsigned n, unsigned shift, unsigned flip,
                      const unsigned *__restrict__ splitters, unsigned nspl, const unsigned *__restrict__ gbase,
-                     unsigned *__restrict__ ticket, unsigned *__restrict__ desc)
+                     unsigned *__restrict__ ticket, unsigned *__restrict__ desc, typename PeerParam<kPeer>::type peer)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     SortSmem      &S    = *reinterpret_cast<SortSmem *>(smem_raw);
     const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned lt = lanemask_lt();
+    if constexpr (kPeer) {
+        if (peer.info[1] != 0) { // some receive buffer is too small: send nothing, keep the exchange sequence aligned
+            peer_finish(S, peer);
+            return;
+        }
+    }
 
     if (tid == 0)
         S.tile = atomicAdd(ticket, 1u);
@@ -528,7 +614,21 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
     __syncthreads();
     SORT_TRACE(tile, 5);
     // ---- out: every digit's run leaves as contiguous stores ---------------------------------------------------
-    if (full) {
+    if constexpr (kPeer) {
+#pragma unroll
+        for (int k = 0; k < kSortItems; k++) {
+            const unsigned j = tid + k * kSortThreads;
+            const unsigned x = S.buf[j];
+            const unsigned d = op(x); // bucket == destination rank
+            const unsigned g = S.gofs[d] + j;
+            if (j < valid) {
+                reinterpret_cast<unsigned *>(peer.k[d])[g] = x;
+                reinterpret_cast<unsigned *>(peer.v[d])[g] = S.vbuf[j];
+            }
+        }
+        peer_finish(S, peer);
+    }
+    else if (full) {
 #pragma unroll
         for (int k = 0; k < kSortItems; k++) {
             const unsigned j = tid + k * kSortThreads;
@@ -570,7 +670,7 @@ static int launch_pass(unsigned tiles, cudaStream_t stream, const unsigned *kin,
         done = true;
     }
     sort_pass_kernel<kBucket, kLB><<<tiles, kSortThreads, sizeof(SortSmem), stream>>>(
-        kin, vin, kout, vout, n, shift, flip, spl, nspl, gbase, ticket, desc);
+        kin, vin, kout, vout, n, shift, flip, spl, nspl, gbase, ticket, desc, NoPeer());
     return (int)cudaGetLastError();
 }
 
@@ -581,6 +681,19 @@ template <bool kBucket, typename... Args> static int launch_pass_lb(Args... args
     if (g_sort_lb <= 4)
         return launch_pass<kBucket, 4>(args...);
     return launch_pass<kBucket, 8>(args...);
+}
+
+// keys[info[0] .. capacity) = pad: the local sort of a receive buffer runs over its whole capacity (no host
+// round trip for the received count); pads order after every real key and, being behind them, after equal ones
+__global__ void fill_tail_kernel(unsigned *__restrict__ keys, unsigned *__restrict__ vals,
+                                 const unsigned *__restrict__ info, unsigned capacity, unsigned pad)
+{
+    const unsigned first = info[0] < capacity ? info[0] : capacity;
+    for (size_t i = first + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < capacity;
+         i += (size_t)gridDim.x * blockDim.x) {
+        keys[i] = pad;
+        vals[i] = 0xffffffffu;
+    }
 }
 
 } // namespace b200
@@ -676,12 +789,86 @@ extern "C" int b200_partition_kv_async(uint32_t *d_dstKey, uint32_t *d_dstVal, c
     if (grid < 1)
         grid = 1;
     sort_hist_kernel<true><<<grid, kSortThreads, 0, stream>>>(d_srcKey, N, flip, d_splitters, nspl, ghist, hticket,
-                                                            d_bucketCounts);
+                                                            d_bucketCounts, NoPeer());
     B200_TRY(cudaGetLastError());
     B200_TRY((cudaError_t)launch_pass_lb<true>(tiles, stream, (const unsigned *)d_srcKey, (const unsigned *)d_srcVal,
                                                d_dstKey, d_dstVal, (unsigned)N, 0u, flip, (const unsigned *)d_splitters,
                                                nspl, (const unsigned *)ghist, tickets, desc));
     count_launch(2);
+    return 0;
+}
+
+// Partition + all-to-all of the multi-GPU sample sort in two kernels and no collective call (b200_p2p_connect
+// first; numBuckets == world, bucket b == rank b).  recvKeys / recvVals: HOST arrays of `world` device pointers,
+// entry r = rank r's receive buffer (capacity pairs each) as mapped into THIS process (b200_p2p_buffer_*).
+// Kernel 1 counts the buckets, exchanges the counts over the peer windows and derives, per destination, where
+// this rank's run starts (sources in rank order => global stability); kernel 2 is the stable partition pass whose
+// digit runs are stored straight into the destination ranks' receive buffers over NVLink, and which ends with a
+// node-wide "all stores are out" exchange.  The tail [received, capacity) of the own receive buffer is padded so
+// that it can be sorted at full capacity.  d_matrix: [world][world] counts (row = source); d_info: [0] pairs
+// received, [1] != 0 when some rank would have received more than `capacity` (then nothing was sent).
+extern "C" int b200_partition_exchange_kv_async(const uint32_t *d_srcKey, const uint32_t *d_srcVal, size_t N,
+                                                const uint32_t *d_splitters, uint32_t sortDir,
+                                                void *const *recvKeys, void *const *recvVals, size_t capacity,
+                                                uint32_t *d_matrix, uint32_t *d_info, b200_stream_t stream_)
+{
+    cudaStream_t   stream = (cudaStream_t)stream_;
+    const P2PArgs *a      = p2p_args();
+    if (!a || a->world < 2 || N >= (1ull << 30) || capacity >= (1ull << 30))
+        return (int)cudaErrorInvalidValue;
+    int        st = 0;
+    DeviceCtx *c  = ctx(&st);
+    if (!c)
+        return st;
+    const unsigned world      = a->world, nspl = world - 1;
+    const unsigned tiles      = (unsigned)((N + kSortTile - 1) / kSortTile);
+    const size_t   desc_bytes = (size_t)(tiles ? tiles : 1) * kRadix * 4;
+    const size_t   need       = kSortOffDesc + desc_bytes;
+    B200_TRY((cudaError_t)ensure(c->sort, need, stream));
+    char *base = reinterpret_cast<char *>(c->sort.ptr);
+    B200_TRY(cudaMemsetAsync(base, 0, need, stream));
+    unsigned *hticket = reinterpret_cast<unsigned *>(base);
+    unsigned *ghist   = reinterpret_cast<unsigned *>(base + kSortOffHist);
+    unsigned *counts  = ghist + kRadix; // second row of the digit table: raw bucket counts (the exchange payload)
+    unsigned *tickets = reinterpret_cast<unsigned *>(base + kSortOffTickets);
+    unsigned *desc    = reinterpret_cast<unsigned *>(base + kSortOffDesc);
+    const unsigned flip = sortDir ? 0u : 0xffffffffu;
+
+    HistPeer hp;
+    hp.p2p      = *a;
+    hp.matrix   = d_matrix;
+    hp.info     = d_info;
+    hp.capacity = (unsigned)capacity;
+    size_t want = (N / 4 + kSortThreads - 1) / kSortThreads;
+    size_t cap  = (size_t)c->num_sms * 4;
+    int    grid = (int)(want < cap ? want : cap);
+    if (grid < 1)
+        grid = 1;
+    sort_hist_kernel<true, true><<<grid, kSortThreads, 0, stream>>>(d_srcKey, N, flip, d_splitters, nspl, ghist,
+                                                                  hticket, counts, hp);
+    B200_TRY(cudaGetLastError());
+    fill_tail_kernel<<<c->num_sms, 1024, 0, stream>>>((unsigned *)recvKeys[a->rank], (unsigned *)recvVals[a->rank],
+                                                     d_info, (unsigned)capacity, ~flip);
+    B200_TRY(cudaGetLastError());
+    SortPeer sp;
+    for (int r = 0; r < kP2PMaxRanks; r++) {
+        sp.k[r] = r < (int)world ? (unsigned long long)(uintptr_t)recvKeys[r] : 0ull;
+        sp.v[r] = r < (int)world ? (unsigned long long)(uintptr_t)recvVals[r] : 0ull;
+    }
+    sp.p2p  = *a;
+    sp.done = tickets + 1;
+    sp.info = d_info;
+    static bool prepared = false;
+    if (!prepared) {
+        B200_TRY(cudaFuncSetAttribute(sort_pass_kernel<true, 4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)sizeof(SortSmem)));
+        prepared = true;
+    }
+    // N == 0: one CTA that only takes part in the closing exchange
+    sort_pass_kernel<true, 4, true><<<tiles ? tiles : 1, kSortThreads, sizeof(SortSmem), stream>>>(
+        d_srcKey, d_srcVal, nullptr, nullptr, (unsigned)N, 0u, flip, d_splitters, nspl, ghist, tickets, desc, sp);
+    B200_TRY(cudaGetLastError());
+    count_launch(3);
     return 0;
 }
 

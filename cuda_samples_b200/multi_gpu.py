@@ -50,8 +50,42 @@ def disable_p2p(group=None):
     if _P2P["world"]:
         torch.cuda.synchronize()
         dist.barrier(group=group)
+        for b in _RECV.values():
+            for r, (k, v) in enumerate(zip(b["keys"], b["vals"])):
+                if r != b["rank"]:
+                    api.p2p_buffer_close(k)
+                    api.p2p_buffer_close(v)
+        dist.barrier(group=group)
+        for b in _RECV.values():
+            api.p2p_buffer_free(b["keys"][b["rank"]])
+            api.p2p_buffer_free(b["vals"][b["rank"]])
+        _RECV.clear()
         api.p2p_disconnect()
         _P2P["world"] = 0
+
+
+_RECV = {}  # n_local -> receive buffers of the fused sort exchange, mapped on every rank
+
+
+def _recv_buffers(n_local, factor, rank, world, group):
+    """Peer-mapped receive buffers for shards of n_local pairs.  The first call for a given n_local is a host
+    collective (max shard size, IPC handles): every rank must reach it together (same sequence of shapes)."""
+    key = (n_local, factor)
+    b = _RECV.get(key)
+    if b is None:
+        biggest = torch.tensor([n_local], dtype=torch.int64, device="cuda")
+        dist.all_reduce(biggest, op=dist.ReduceOp.MAX, group=group)
+        capacity = (int(int(biggest.item()) * factor) + 2 * 8192 - 1) // 8192 * 8192
+        kp, kh = api.p2p_buffer_create(4 * capacity)
+        vp, vh = api.p2p_buffer_create(4 * capacity)
+        handles = [None] * world
+        dist.all_gather_object(handles, (kh, vh), group=group)
+        b = {"rank": rank, "capacity": capacity,
+             "keys": [kp if r == rank else api.p2p_buffer_open(handles[r][0]) for r in range(world)],
+             "vals": [vp if r == rank else api.p2p_buffer_open(handles[r][1]) for r in range(world)]}
+        dist.barrier(group=group)
+        _RECV[key] = b
+    return b
 
 
 def p2p_enabled():
@@ -247,9 +281,12 @@ def choose_splitters(samples_ordered, world):
     return s[idx]
 
 
-def sort_sharded(keys, vals, n_local, direction=1, ops=None, group=None, samples_per_rank=1024):
+def sort_sharded(keys, vals, n_local, direction=1, ops=None, group=None, samples_per_rank=1024, capacity_factor=1.125):
     """Stable global key-value sort.  Rank r ends up with the r-th key range (ascending ranges for
-    direction=1, descending for 0).  -> (keys_out, vals_out, n_out, counts_matrix)."""
+    direction=1, descending for 0).  -> (keys_out, vals_out, n_out, counts_matrix).
+    With enable_p2p() the partition pass stores every bucket straight into its destination rank's receive buffer
+    over NVLink (no all-to-all, no host round trip before the local sort); a receive buffer holds
+    capacity_factor x the largest shard, and a distribution that overflows it falls back to the NCCL path."""
     ops = ops or CudaOps()
     rank, world = _world(group)
     if world == 1:
@@ -268,6 +305,20 @@ def sort_sharded(keys, vals, n_local, direction=1, ops=None, group=None, samples
     dist.all_gather_into_tensor(gathered, local.contiguous(), group=group)
     spl64 = choose_splitters(gathered, world)
     spl = torch.where(spl64 >= 2**31, spl64 - 2**32, spl64).to(torch.int32).contiguous()
+    if p2p_enabled() and isinstance(ops, CudaOps) and world == _P2P["world"]:
+        # 2-4 fused: count + exchange of counts, partition pass that scatters into the peers' receive buffers
+        b = _recv_buffers(n_local, capacity_factor, rank, world, group)
+        cap = b["capacity"]
+        meta = torch.empty(world * world + 2, dtype=torch.int32, device=keys.device)
+        api.partition_exchange_kv(keys, vals, n_local, spl, direction, b["keys"], b["vals"], cap,
+                                  meta[:world * world], meta[world * world:])
+        # 5. local stable sort of the whole (padded) receive buffer: no host round trip for the received count
+        dk, dv, bk, bv = (torch.empty(cap, dtype=torch.int32, device=keys.device) for _ in range(4))
+        api.mergeSort(dk, dv, bk, bv, b["keys"][rank], b["vals"][rank], cap, direction)
+        host = meta.cpu()  # the only synchronisation: after everything is queued
+        if int(host[-1]) == 0:
+            return dk, dv, int(host[-2]), host[:world * world].reshape(world, world)
+        # some rank would receive more than `cap` pairs: nothing was sent, every rank takes the NCCL path below
     # 2. local stable partition into `world` buckets
     pk, pv, counts = ops.partition(keys, vals, n_local, spl, world, direction)
     # 3. everyone learns everyone's bucket sizes

@@ -124,6 +124,20 @@ int b200_reduce_partial_exchange_async(int kind, const void *d_in, size_t n, dou
 /* sharded long scan, step 1: shard total -> peers -> *d_carry; d_work: >= 2 + world doubles of scratch */
 int b200_scan_total_exchange_async(uint32_t *d_carry, const uint32_t *d_src, size_t n, double *d_work,
                                    b200_stream_t stream);
+/* large peer-mapped buffers (cudaMalloc + CUDA IPC): create locally, open the peers' handles */
+int b200_p2p_buffer_create(size_t bytes, void **d_ptr, unsigned char *handle_out /* 64 bytes */);
+int b200_p2p_buffer_open(const unsigned char *handle, void **d_peer);
+int b200_p2p_buffer_close(void *d_peer);
+int b200_p2p_buffer_free(void *d_ptr);
+/* partition + all-to-all of the multi-GPU sample sort without a collective call: bucket b == rank b, the stable
+ * partition pass stores every bucket's run straight into rank b's receive buffer over NVLink.  recvKeys/recvVals:
+ * HOST arrays of `world` device pointers (rank r's receive buffer as mapped here), `capacity` pairs each.  The own
+ * buffer's tail [received, capacity) is padded so it can be sorted at full capacity.  d_matrix [world][world]
+ * (row = source rank), d_info[0] = pairs received, d_info[1] != 0: a buffer would overflow, nothing was sent. */
+int b200_partition_exchange_kv_async(const uint32_t *d_srcKey, const uint32_t *d_srcVal, size_t N,
+                                     const uint32_t *d_splitters, uint32_t sortDir, void *const *recvKeys,
+                                     void *const *recvVals, size_t capacity, uint32_t *d_matrix, uint32_t *d_info,
+                                     b200_stream_t stream);
 /* histogram64 + histogram256 of the concatenation of all ranks' shards, on every rank, one kernel per rank */
 int b200_histogram_fused_allreduce_async(uint32_t *d_hist256, uint32_t *d_hist64, const void *d_data,
                                          size_t byteCount, b200_stream_t stream);

@@ -94,18 +94,31 @@ def main():
 
     # sort: world * 2^22 pairs, three datasets, both directions
     n = 1 << 22
-    for kind, param in (("key_unique", 0), ("key_tile_unique", 1 << 12), ("key_mod", 1000)):
-        keys = oracle.generate(kind, 0, world * n, 7, param)
-        vals = np.arange(world * n, dtype=np.uint32)
-        for direction in (1, 0):
-            sk = torch.from_numpy(keys[rank * n:(rank + 1) * n].view(np.int32).copy()).cuda()
-            sv = torch.from_numpy(vals[rank * n:(rank + 1) * n].view(np.int32).copy()).cuda()
-            dk, dv, n_out, m = mg.sort_sharded(sk, sv, n, direction)
-            wk, wv = oracle.stable_sort_kv(keys, vals, direction)
-            off = int(m[:, :rank].sum())  # rows = source, cols = destination: everything sent to lower ranks
-            gk, gv = dk[:n_out].cpu().numpy().view(np.uint32), dv[:n_out].cpu().numpy().view(np.uint32)
-            check("sort %s dir=%d" % (kind, direction),
-                  int(m.sum()) == world * n and (gk == wk[off:off + n_out]).all() and (gv == wv[off:off + n_out]).all())
+
+    def sort_checks(tag, **kw):
+        for kind, param in (("key_unique", 0), ("key_tile_unique", 1 << 12), ("key_mod", 1000)):
+            keys = oracle.generate(kind, 0, world * n, 7, param)
+            vals = np.arange(world * n, dtype=np.uint32)
+            for direction in (1, 0):
+                sk = torch.from_numpy(keys[rank * n:(rank + 1) * n].view(np.int32).copy()).cuda()
+                sv = torch.from_numpy(vals[rank * n:(rank + 1) * n].view(np.int32).copy()).cuda()
+                dk, dv, n_out, m = mg.sort_sharded(sk, sv, n, direction, **kw)
+                wk, wv = oracle.stable_sort_kv(keys, vals, direction)
+                off = int(m[:, :rank].sum())  # rows = source, cols = destination: everything sent to lower ranks
+                gk, gv = dk[:n_out].cpu().numpy().view(np.uint32), dv[:n_out].cpu().numpy().view(np.uint32)
+                check("%s sort %s dir=%d" % (tag, kind, direction), int(m.sum()) == world * n and
+                      (gk == wk[off:off + n_out]).all() and (gv == wv[off:off + n_out]).all())
+
+    sort_checks("nccl:")
+    # partition pass storing straight into the peers' receive buffers (twice: the buffers are reused), and with
+    # receive buffers that are too small: every rank must fall back to the NCCL path with the same result
+    mg.enable_p2p()
+    sort_checks("p2p:")
+    sort_checks("p2p again:")
+    sort_checks("p2p overflow->fallback:", capacity_factor=0.5)
+    torch.cuda.synchronize()
+    check("p2p_errors after sort", prim.p2p_errors() == 0)
+    mg.disable_p2p()
 
     flag = torch.tensor([len(failures)], dtype=torch.int32, device="cuda")
     dist.all_reduce(flag)
