@@ -284,7 +284,9 @@ def primitives_table(torch, dist, prim, mg, rank, world, peak, barrier, p2p=Fals
         "frac_of_measured_peak": round(68 * N_ELEMS / t / 1e9 / (peak * world), 4),
         "frac_of_nominal_8TBs": round(68 * N_ELEMS / t / 1e9 / (HBM_NOMINAL * world), 4),
         "scaling": "strong", "dataset": "D1 unique keys, val=i, ascending",
-        "collective": "sample sort: all_gather + all_to_all" if world > 1 else None}
+        "collective": (("sample sort: all_gather of samples (NCCL) + partition pass storing into the peers' receive "
+                        "buffers over NVLink (no all-to-all call)") if p2p else
+                       "sample sort: all_gather + all_to_all") if world > 1 else None}
     return table
 
 

@@ -33,6 +33,7 @@ SIGNATURES = {
     "b200_scan_exclusive_async": (ci, [vp, vp, sz, sz, vp, vp]),
     "b200_scan_total_async": (ci, [vp, vp, sz, vp]),
     "b200_sort_kv_async": (ci, [vp, vp, vp, vp, vp, vp, sz, u32, vp]),
+    "b200_sort_kv_dyn_async": (ci, [vp, vp, vp, vp, vp, vp, sz, vp, u32, vp]),
     "b200_partition_kv_async": (ci, [vp, vp, vp, vp, sz, vp, u32, u32, vp, vp]),
     "b200_segmented_sort_kv_async": (ci, [vp, vp, vp, vp, sz, sz, u32, vp]),
     "b200_generate_async": (ci, [vp, sz, sz, u64, ci, u32, vp]),

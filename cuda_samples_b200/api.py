@@ -276,6 +276,12 @@ def mergeSort(dstKey, dstVal, bufKey, bufVal, srcKey, srcVal, N, sortDir, stream
                                  _dptr(srcVal), N, sortDir, _stream(stream)), "mergeSort")
 
 
+def sort_kv_dyn(dstKey, dstVal, bufKey, bufVal, srcKey, srcVal, capacity, d_n, sortDir, stream=None):
+    """mergeSort over the first min(d_n[0], capacity) pairs, d_n read on the device (no host round trip)."""
+    check(lib.b200_sort_kv_dyn_async(_dptr(dstKey), _dptr(dstVal), _dptr(bufKey), _dptr(bufVal), _dptr(srcKey),
+                                     _dptr(srcVal), capacity, _dptr(d_n), sortDir, _stream(stream)), "sort_kv_dyn")
+
+
 def bitonicSort(d_DstKey, d_DstVal, d_SrcKey, d_SrcVal, batchSize, arrayLength, dir, stream=None):
     """sortingNetworks sample: batchSize independent key-value sorts of arrayLength pairs (stable, any length)."""
     check(lib.b200_segmented_sort_kv_async(_dptr(d_DstKey), _dptr(d_DstVal), _dptr(d_SrcKey), _dptr(d_SrcVal),

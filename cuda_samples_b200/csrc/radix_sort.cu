@@ -301,8 +301,10 @@ constexpr int kHist4Threads = 1024;
 
 __global__ void __launch_bounds__(kHist4Threads, 1)
     sort_hist4_kernel(const unsigned *__restrict__ keys, size_t n, unsigned flip, unsigned *__restrict__ ghist,
-                      unsigned *__restrict__ ticket)
+                      unsigned *__restrict__ ticket, const unsigned *__restrict__ n_dev)
 {
+    if (n_dev) // pair count produced on the device (receive buffer of the multi-GPU sort); n is its capacity
+        n = *n_dev < n ? *n_dev : n;
     extern __shared__ __align__(16) unsigned tab[]; // [4][256][32]
     __shared__ bool s_last;
     const unsigned  lane = threadIdx.x & 31, warp = threadIdx.x >> 5, lane4 = lane * 4;
@@ -421,8 +423,14 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
     sort_pass_kernel(const unsigned *__restrict__ kin, const unsigned *__restrict__ vin, unsigned *__restrict__ kout,
                      unsigned *__restrict__ vout, unsigned n, unsigned shift, unsigned flip,
                      const unsigned *__restrict__ splitters, unsigned nspl, const unsigned *__restrict__ gbase,
-                     unsigned *__restrict__ ticket, unsigned *__restrict__ desc, typename PeerParam<kPeer>::type peer)
+                     unsigned *__restrict__ ticket, unsigned *__restrict__ desc, typename PeerParam<kPeer>::type peer,
+                     const unsigned *__restrict__ n_dev)
 {
+    if (n_dev) { // device-side pair count: the grid covers the capacity, CTAs beyond the data leave at once
+        n = *n_dev < n ? *n_dev : n;
+        if ((size_t)blockIdx.x * kSortTile >= n)
+            return; // (tickets are only drawn by CTAs that have a tile: tiles stay dense in ticket order)
+    }
     extern __shared__ __align__(16) unsigned char smem_raw[];
     SortSmem      &S    = *reinterpret_cast<SortSmem *>(smem_raw);
     const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -661,7 +669,7 @@ static int g_sort_lb = 4; // look-back descriptors fetched per round trip (1, 4 
 template <bool kBucket, int kLB>
 static int launch_pass(unsigned tiles, cudaStream_t stream, const unsigned *kin, const unsigned *vin, unsigned *kout,
                        unsigned *vout, unsigned n, unsigned shift, unsigned flip, const unsigned *spl, unsigned nspl,
-                       const unsigned *gbase, unsigned *ticket, unsigned *desc)
+                       const unsigned *gbase, unsigned *ticket, unsigned *desc, const unsigned *n_dev)
 {
     static bool done = false;
     if (!done) {
@@ -670,7 +678,7 @@ static int launch_pass(unsigned tiles, cudaStream_t stream, const unsigned *kin,
         done = true;
     }
     sort_pass_kernel<kBucket, kLB><<<tiles, kSortThreads, sizeof(SortSmem), stream>>>(
-        kin, vin, kout, vout, n, shift, flip, spl, nspl, gbase, ticket, desc, NoPeer());
+        kin, vin, kout, vout, n, shift, flip, spl, nspl, gbase, ticket, desc, NoPeer(), n_dev);
     return (int)cudaGetLastError();
 }
 
@@ -683,26 +691,13 @@ template <bool kBucket, typename... Args> static int launch_pass_lb(Args... args
     return launch_pass<kBucket, 8>(args...);
 }
 
-// keys[info[0] .. capacity) = pad: the local sort of a receive buffer runs over its whole capacity (no host
-// round trip for the received count); pads order after every real key and, being behind them, after equal ones
-__global__ void fill_tail_kernel(unsigned *__restrict__ keys, unsigned *__restrict__ vals,
-                                 const unsigned *__restrict__ info, unsigned capacity, unsigned pad)
-{
-    const unsigned first = info[0] < capacity ? info[0] : capacity;
-    for (size_t i = first + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < capacity;
-         i += (size_t)gridDim.x * blockDim.x) {
-        keys[i] = pad;
-        vals[i] = 0xffffffffu;
-    }
-}
-
 } // namespace b200
 
 using namespace b200;
 
-extern "C" int b200_sort_kv_async(uint32_t *d_dstKey, uint32_t *d_dstVal, uint32_t *d_bufKey, uint32_t *d_bufVal,
-                                  const uint32_t *d_srcKey, const uint32_t *d_srcVal, size_t N, uint32_t sortDir,
-                                  b200_stream_t stream_)
+static int sort_kv(uint32_t *d_dstKey, uint32_t *d_dstVal, uint32_t *d_bufKey, uint32_t *d_bufVal,
+                   const uint32_t *d_srcKey, const uint32_t *d_srcVal, size_t N, uint32_t sortDir,
+                   const uint32_t *d_n, b200_stream_t stream_)
 {
     cudaStream_t stream = (cudaStream_t)stream_;
     if (N == 0)
@@ -735,7 +730,8 @@ extern "C" int b200_sort_kv_async(uint32_t *d_dstKey, uint32_t *d_dstVal, uint32
         int    grid = (int)(want < (size_t)c->num_sms ? want : (size_t)c->num_sms);
         if (grid < 1)
             grid = 1;
-        sort_hist4_kernel<<<grid, kHist4Threads, 4 * kRadix * 32 * 4, stream>>>(d_srcKey, N, flip, ghist, hticket);
+        sort_hist4_kernel<<<grid, kHist4Threads, 4 * kRadix * 32 * 4, stream>>>(d_srcKey, N, flip, ghist, hticket,
+                                                                                d_n);
         B200_TRY(cudaGetLastError());
     }
 
@@ -746,12 +742,31 @@ extern "C" int b200_sort_kv_async(uint32_t *d_dstKey, uint32_t *d_dstVal, uint32
         unsigned *desc = reinterpret_cast<unsigned *>(base + kSortOffDesc + p * desc_bytes);
         B200_TRY((cudaError_t)launch_pass_lb<false>(tiles, stream, kin, vin, kout, vout, (unsigned)N, 8u * p, flip,
                                                     (const unsigned *)nullptr, 0u, (const unsigned *)(ghist + p * kRadix),
-                                                    tickets + p, desc));
+                                                    tickets + p, desc, (const unsigned *)d_n));
         kin = kout;
         vin = vout;
     }
     count_launch(5);
     return 0;
+}
+
+extern "C" int b200_sort_kv_async(uint32_t *d_dstKey, uint32_t *d_dstVal, uint32_t *d_bufKey, uint32_t *d_bufVal,
+                                  const uint32_t *d_srcKey, const uint32_t *d_srcVal, size_t N, uint32_t sortDir,
+                                  b200_stream_t stream)
+{
+    return sort_kv(d_dstKey, d_dstVal, d_bufKey, d_bufVal, d_srcKey, d_srcVal, N, sortDir, nullptr, stream);
+}
+
+// The same with the pair count read on the device: sorts the first min(*d_n, capacity) pairs; the launch geometry
+// and the scratch are sized for `capacity`.  Lets the multi-GPU sort run on a receive buffer whose fill level only
+// the GPU knows yet (no host round trip between the exchange and the local sort).
+extern "C" int b200_sort_kv_dyn_async(uint32_t *d_dstKey, uint32_t *d_dstVal, uint32_t *d_bufKey, uint32_t *d_bufVal,
+                                      const uint32_t *d_srcKey, const uint32_t *d_srcVal, size_t capacity,
+                                      const uint32_t *d_n, uint32_t sortDir, b200_stream_t stream)
+{
+    if (!d_n)
+        return (int)cudaErrorInvalidValue;
+    return sort_kv(d_dstKey, d_dstVal, d_bufKey, d_bufVal, d_srcKey, d_srcVal, capacity, sortDir, d_n, stream);
 }
 
 extern "C" int b200_partition_kv_async(uint32_t *d_dstKey, uint32_t *d_dstVal, const uint32_t *d_srcKey,
@@ -793,7 +808,7 @@ extern "C" int b200_partition_kv_async(uint32_t *d_dstKey, uint32_t *d_dstVal, c
     B200_TRY(cudaGetLastError());
     B200_TRY((cudaError_t)launch_pass_lb<true>(tiles, stream, (const unsigned *)d_srcKey, (const unsigned *)d_srcVal,
                                                d_dstKey, d_dstVal, (unsigned)N, 0u, flip, (const unsigned *)d_splitters,
-                                               nspl, (const unsigned *)ghist, tickets, desc));
+                                               nspl, (const unsigned *)ghist, tickets, desc, (const unsigned *)nullptr));
     count_launch(2);
     return 0;
 }
@@ -804,8 +819,8 @@ extern "C" int b200_partition_kv_async(uint32_t *d_dstKey, uint32_t *d_dstVal, c
 // Kernel 1 counts the buckets, exchanges the counts over the peer windows and derives, per destination, where
 // this rank's run starts (sources in rank order => global stability); kernel 2 is the stable partition pass whose
 // digit runs are stored straight into the destination ranks' receive buffers over NVLink, and which ends with a
-// node-wide "all stores are out" exchange.  The tail [received, capacity) of the own receive buffer is padded so
-// that it can be sorted at full capacity.  d_matrix: [world][world] counts (row = source); d_info: [0] pairs
+// node-wide "all stores are out" exchange.  The local sort then runs with the received count read on the device
+// (b200_sort_kv_dyn_async, d_n = d_info).  d_matrix: [world][world] counts (row = source); d_info: [0] pairs
 // received, [1] != 0 when some rank would have received more than `capacity` (then nothing was sent).
 extern "C" int b200_partition_exchange_kv_async(const uint32_t *d_srcKey, const uint32_t *d_srcVal, size_t N,
                                                 const uint32_t *d_splitters, uint32_t sortDir,
@@ -847,9 +862,6 @@ extern "C" int b200_partition_exchange_kv_async(const uint32_t *d_srcKey, const 
     sort_hist_kernel<true, true><<<grid, kSortThreads, 0, stream>>>(d_srcKey, N, flip, d_splitters, nspl, ghist,
                                                                   hticket, counts, hp);
     B200_TRY(cudaGetLastError());
-    fill_tail_kernel<<<c->num_sms, 1024, 0, stream>>>((unsigned *)recvKeys[a->rank], (unsigned *)recvVals[a->rank],
-                                                     d_info, (unsigned)capacity, ~flip);
-    B200_TRY(cudaGetLastError());
     SortPeer sp;
     for (int r = 0; r < kP2PMaxRanks; r++) {
         sp.k[r] = r < (int)world ? (unsigned long long)(uintptr_t)recvKeys[r] : 0ull;
@@ -866,9 +878,10 @@ extern "C" int b200_partition_exchange_kv_async(const uint32_t *d_srcKey, const 
     }
     // N == 0: one CTA that only takes part in the closing exchange
     sort_pass_kernel<true, 4, true><<<tiles ? tiles : 1, kSortThreads, sizeof(SortSmem), stream>>>(
-        d_srcKey, d_srcVal, nullptr, nullptr, (unsigned)N, 0u, flip, d_splitters, nspl, ghist, tickets, desc, sp);
+        d_srcKey, d_srcVal, nullptr, nullptr, (unsigned)N, 0u, flip, d_splitters, nspl, ghist, tickets, desc, sp,
+        nullptr);
     B200_TRY(cudaGetLastError());
-    count_launch(3);
+    count_launch(2);
     return 0;
 }
 

@@ -281,7 +281,7 @@ def choose_splitters(samples_ordered, world):
     return s[idx]
 
 
-def sort_sharded(keys, vals, n_local, direction=1, ops=None, group=None, samples_per_rank=1024, capacity_factor=1.125):
+def sort_sharded(keys, vals, n_local, direction=1, ops=None, group=None, samples_per_rank=1024, capacity_factor=1.25):
     """Stable global key-value sort.  Rank r ends up with the r-th key range (ascending ranges for
     direction=1, descending for 0).  -> (keys_out, vals_out, n_out, counts_matrix).
     With enable_p2p() the partition pass stores every bucket straight into its destination rank's receive buffer
@@ -312,9 +312,9 @@ def sort_sharded(keys, vals, n_local, direction=1, ops=None, group=None, samples
         meta = torch.empty(world * world + 2, dtype=torch.int32, device=keys.device)
         api.partition_exchange_kv(keys, vals, n_local, spl, direction, b["keys"], b["vals"], cap,
                                   meta[:world * world], meta[world * world:])
-        # 5. local stable sort of the whole (padded) receive buffer: no host round trip for the received count
+        # 5. local stable sort of the receive buffer, received count read on the device: no host round trip
         dk, dv, bk, bv = (torch.empty(cap, dtype=torch.int32, device=keys.device) for _ in range(4))
-        api.mergeSort(dk, dv, bk, bv, b["keys"][rank], b["vals"][rank], cap, direction)
+        api.sort_kv_dyn(dk, dv, bk, bv, b["keys"][rank], b["vals"][rank], cap, meta[world * world:], direction)
         host = meta.cpu()  # the only synchronisation: after everything is queued
         if int(host[-1]) == 0:
             return dk, dv, int(host[-2]), host[:world * world].reshape(world, world)

@@ -129,10 +129,16 @@ int b200_p2p_buffer_create(size_t bytes, void **d_ptr, unsigned char *handle_out
 int b200_p2p_buffer_open(const unsigned char *handle, void **d_peer);
 int b200_p2p_buffer_close(void *d_peer);
 int b200_p2p_buffer_free(void *d_ptr);
+/* b200_sort_kv_async with the pair count read on the device: sorts the first min(*d_n, capacity) pairs; geometry
+ * and scratch are sized for `capacity`.  (The multi-GPU sort runs it on a receive buffer whose fill level only the
+ * GPU knows yet.) */
+int b200_sort_kv_dyn_async(uint32_t *d_dstKey, uint32_t *d_dstVal, uint32_t *d_bufKey, uint32_t *d_bufVal,
+                           const uint32_t *d_srcKey, const uint32_t *d_srcVal, size_t capacity, const uint32_t *d_n,
+                           uint32_t sortDir, b200_stream_t stream);
 /* partition + all-to-all of the multi-GPU sample sort without a collective call: bucket b == rank b, the stable
  * partition pass stores every bucket's run straight into rank b's receive buffer over NVLink.  recvKeys/recvVals:
- * HOST arrays of `world` device pointers (rank r's receive buffer as mapped here), `capacity` pairs each.  The own
- * buffer's tail [received, capacity) is padded so it can be sorted at full capacity.  d_matrix [world][world]
+ * HOST arrays of `world` device pointers (rank r's receive buffer as mapped here), `capacity` pairs each.
+ * d_matrix [world][world]
  * (row = source rank), d_info[0] = pairs received, d_info[1] != 0: a buffer would overflow, nothing was sent. */
 int b200_partition_exchange_kv_async(const uint32_t *d_srcKey, const uint32_t *d_srcVal, size_t N,
                                      const uint32_t *d_splitters, uint32_t sortDir, void *const *recvKeys,
