@@ -49,6 +49,7 @@ SIGNATURES = {
     "b200_p2p_disconnect": (ci, []),
     "b200_p2p_world": (ci, []),
     "b200_p2p_errors": (ci, [ctypes.POINTER(ctypes.c_ulonglong)]),
+    "b200_p2p_barrier_async": (ci, [vp]),
     "b200_p2p_allgather_async": (ci, [vp, sz, vp, vp]),
     "b200_reduce_partial_exchange_async": (ci, [ci, vp, sz, vp, ctypes.c_uint, ctypes.c_uint, vp, vp, vp, vp]),
     "b200_scan_total_exchange_async": (ci, [vp, vp, sz, vp, vp]),

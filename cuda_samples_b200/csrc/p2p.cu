@@ -50,6 +50,22 @@ __global__ void __launch_bounds__(256, 1)
     }
 }
 
+// Node-wide barrier on the stream: everything this rank enqueued before it (peer stores included) has completed
+// when the kernel starts; it then tells every peer and returns once every peer has said the same.
+__global__ void __launch_bounds__(32, 1) p2p_barrier_kernel(P2PArgs a)
+{
+    __shared__ unsigned long long s_seq;
+    __shared__ unsigned           s_token;
+    if (threadIdx.x == 0)
+        s_token = 1;
+    __syncthreads();
+    __threadfence_system();
+    const unsigned seq = p2p_exchange(a, &s_token, 1, &s_seq);
+    if (threadIdx.x < a.world)
+        (void)p2p_peer_word(a, seq, threadIdx.x, 0);
+    __threadfence_system();
+}
+
 } // namespace b200
 
 using namespace b200;
@@ -169,5 +185,16 @@ extern "C" int b200_p2p_buffer_close(void *d_peer)
 extern "C" int b200_p2p_buffer_free(void *d_ptr)
 {
     B200_TRY(cudaFree(d_ptr));
+    return 0;
+}
+
+extern "C" int b200_p2p_barrier_async(b200_stream_t stream)
+{
+    const P2PArgs *a = p2p_args();
+    if (!a || a->world == 0)
+        return (int)cudaErrorInvalidValue;
+    p2p_barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(*a);
+    count_launch();
+    B200_TRY(cudaGetLastError());
     return 0;
 }

@@ -71,16 +71,12 @@ struct SortSmem {
     unsigned wsum[kRadix / 32];
     unsigned splitters[kRadix];
     unsigned tile;
-    unsigned token;                 // peer variant: payload of the "all my stores are out" exchange
-    unsigned long long p2p_seq;
 };
 
 // Peer variant of the partition (multi-GPU sample sort): bucket b IS rank b, and its run is stored straight into
 // rank b's receive buffer over NVLink instead of into a local array that an all-to-all would copy again.
 struct SortPeer {
     unsigned long long k[kP2PMaxRanks], v[kP2PMaxRanks]; // receive buffers of every rank (peer-mapped)
-    P2PArgs            p2p;
-    unsigned          *done;   // CTAs of this launch whose stores are fenced
     const unsigned    *info;   // [0] n_out, [1] != 0: a receive buffer would overflow -> nothing is sent
 };
 struct NoPeer {};
@@ -396,28 +392,6 @@ __global__ void __launch_bounds__(kHist4Threads, 1)
 //   * keys go to shared memory as soon as the bases are known; the values are loaded only then (their latency
 //     hides behind the look-back), so that at most 32 payload registers are live and nothing spills.
 // ---------------------------------------------------------------------------------------------------
-// All stores of this CTA are fenced; the last CTA of the launch tells every peer and waits for every peer's word:
-// when the kernel ends on a rank, that rank's receive buffer is complete.
-__device__ __forceinline__ void peer_finish(SortSmem &S, const SortPeer &peer)
-{
-    __shared__ bool s_last;
-    __threadfence_system();
-    __syncthreads();
-    if (threadIdx.x == 0)
-        s_last = atomicAdd(peer.done, 1u) == gridDim.x - 1;
-    __syncthreads();
-    if (!s_last)
-        return;
-    __threadfence_system();
-    if (threadIdx.x == 0)
-        S.token = 1;
-    __syncthreads();
-    const unsigned seq = p2p_exchange(peer.p2p, &S.token, 1, &S.p2p_seq);
-    if (threadIdx.x < peer.p2p.world)
-        (void)p2p_peer_word(peer.p2p, seq, threadIdx.x, 0);
-    __threadfence_system();
-}
-
 template <bool kBucket, int kLB, bool kPeer = false>
 __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
     sort_pass_kernel(const unsigned *__restrict__ kin, const unsigned *__restrict__ vin, unsigned *__restrict__ kout,
@@ -436,10 +410,8 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
     const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned lt = lanemask_lt();
     if constexpr (kPeer) {
-        if (peer.info[1] != 0) { // some receive buffer is too small: send nothing, keep the exchange sequence aligned
-            peer_finish(S, peer);
+        if (peer.info[1] != 0) // some receive buffer is too small: send nothing (the caller falls back)
             return;
-        }
     }
 
     if (tid == 0)
@@ -634,7 +606,6 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
                 reinterpret_cast<unsigned *>(peer.v[d])[g] = S.vbuf[j];
             }
         }
-        peer_finish(S, peer);
     }
     else if (full) {
 #pragma unroll
@@ -818,8 +789,8 @@ extern "C" int b200_partition_kv_async(uint32_t *d_dstKey, uint32_t *d_dstVal, c
 // entry r = rank r's receive buffer (capacity pairs each) as mapped into THIS process (b200_p2p_buffer_*).
 // Kernel 1 counts the buckets, exchanges the counts over the peer windows and derives, per destination, where
 // this rank's run starts (sources in rank order => global stability); kernel 2 is the stable partition pass whose
-// digit runs are stored straight into the destination ranks' receive buffers over NVLink, and which ends with a
-// node-wide "all stores are out" exchange.  The local sort then runs with the received count read on the device
+// digit runs are stored straight into the destination ranks' receive buffers over NVLink; a node-wide barrier kernel
+// follows it on the stream ("all my stores are out").  The local sort then runs with the received count read on the device
 // (b200_sort_kv_dyn_async, d_n = d_info).  d_matrix: [world][world] counts (row = source); d_info: [0] pairs
 // received, [1] != 0 when some rank would have received more than `capacity` (then nothing was sent).
 extern "C" int b200_partition_exchange_kv_async(const uint32_t *d_srcKey, const uint32_t *d_srcVal, size_t N,
@@ -867,8 +838,6 @@ extern "C" int b200_partition_exchange_kv_async(const uint32_t *d_srcKey, const 
         sp.k[r] = r < (int)world ? (unsigned long long)(uintptr_t)recvKeys[r] : 0ull;
         sp.v[r] = r < (int)world ? (unsigned long long)(uintptr_t)recvVals[r] : 0ull;
     }
-    sp.p2p  = *a;
-    sp.done = tickets + 1;
     sp.info = d_info;
     static bool prepared = false;
     if (!prepared) {
@@ -882,7 +851,9 @@ extern "C" int b200_partition_exchange_kv_async(const uint32_t *d_srcKey, const 
         nullptr);
     B200_TRY(cudaGetLastError());
     count_launch(2);
-    return 0;
+    // The pass kernel's peer stores are complete when it ends (no per-CTA system fence inside: that stalled every
+    // tile for an NVLink round trip); a one-CTA kernel behind it then tells every peer and waits for every peer.
+    return b200_p2p_barrier_async(stream_);
 }
 
 // tuning knob for experiments (not part of the stable ABI)

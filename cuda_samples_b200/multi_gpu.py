@@ -313,7 +313,10 @@ def sort_sharded(keys, vals, n_local, direction=1, ops=None, group=None, samples
         api.partition_exchange_kv(keys, vals, n_local, spl, direction, b["keys"], b["vals"], cap,
                                   meta[:world * world], meta[world * world:])
         # 5. local stable sort of the receive buffer, received count read on the device: no host round trip
-        dk, dv, bk, bv = (torch.empty(cap, dtype=torch.int32, device=keys.device) for _ in range(4))
+        dk, dv = (torch.empty(cap, dtype=torch.int32, device=keys.device) for _ in range(2))
+        if "scratch" not in b:  # ping-pong scratch of the local sort lives with the receive buffers
+            b["scratch"] = [torch.empty(cap, dtype=torch.int32, device=keys.device) for _ in range(2)]
+        bk, bv = b["scratch"]
         api.sort_kv_dyn(dk, dv, bk, bv, b["keys"][rank], b["vals"][rank], cap, meta[world * world:], direction)
         host = meta.cpu()  # the only synchronisation: after everything is queued
         if int(host[-1]) == 0:

@@ -114,6 +114,9 @@ int b200_p2p_world(void); /* 0 until connected */
 int b200_p2p_errors(unsigned long long *count);
 /* d_gathered[r * nbytes ..) = rank r's payload on every rank; nbytes % 4 == 0, <= 2048 */
 int b200_p2p_allgather_async(const void *d_payload, size_t nbytes, void *d_gathered, b200_stream_t stream);
+/* node-wide barrier on the stream: returns (stream order) once every rank's earlier work, peer stores included,
+ * has completed */
+int b200_p2p_barrier_async(b200_stream_t stream);
 /* reduce -> exchange: d_slots[0..count) are this rank's shard partials (b200_reduce_partial_async fills the
  * others, this launch fills [index]); on every rank d_gathered[r*count + k] = rank r's slot k and
  * d_sums[k] = sum over ranks in rank order (fp64, deterministic).  d_carry (nullable) = wrapping u32 sum of slot

@@ -1,0 +1,60 @@
+#!/usr/bin/env python3
+"""Where the time of the multi-GPU sort goes (CUDA events per phase, rank 0 prints).  Launch under torchrun:
+    python -m torch.distributed.run --nproc-per-node G profiles/sort_sharded_phases.py"""
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import cuda_samples_b200 as prim  # noqa: E402
+from cuda_samples_b200 import api, multi_gpu as mg  # noqa: E402
+
+rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local)
+dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+mg.enable_p2p()
+n = (1 << 28) // world
+sk = torch.empty(n, dtype=torch.int32, device="cuda")
+sv = torch.arange(rank * n, rank * n + n, dtype=torch.int64, device="cuda").to(torch.int32)
+prim.generate(sk, "key_unique", rank * n, n, 2009)
+for _ in range(3):
+    mg.sort_sharded(sk, sv, n, 1)
+b = mg._recv_buffers(n, 1.25, rank, world, None)
+cap = b["capacity"]
+ev = [torch.cuda.Event(enable_timing=True) for _ in range(6)]
+acc = [0.0] * 5
+REPS = 5
+for _ in range(REPS):
+    torch.cuda.synchronize()
+    dist.barrier()
+    torch.cuda.synchronize()
+    ev[0].record()
+    ns = 1024
+    step = max(n // ns, 1)
+    loc = (sk[:n:step][:ns].to(torch.int64) & 0xFFFFFFFF)
+    gathered = torch.empty(world * ns, dtype=torch.int64, device="cuda")
+    dist.all_gather_into_tensor(gathered, loc.contiguous())
+    spl64 = mg.choose_splitters(gathered, world)
+    spl = torch.where(spl64 >= 2**31, spl64 - 2**32, spl64).to(torch.int32).contiguous()
+    ev[1].record()
+    meta = torch.empty(world * world + 2, dtype=torch.int32, device="cuda")
+    api.partition_exchange_kv(sk, sv, n, spl, 1, b["keys"], b["vals"], cap, meta[:world * world], meta[world * world:])
+    ev[2].record()
+    dk, dv, bk, bv = (torch.empty(cap, dtype=torch.int32, device="cuda") for _ in range(4))
+    ev[3].record()
+    api.sort_kv_dyn(dk, dv, bk, bv, b["keys"][rank], b["vals"][rank], cap, meta[world * world:], 1)
+    ev[4].record()
+    host = meta.cpu()
+    ev[5].record()
+    torch.cuda.synchronize()
+    for i in range(5):
+        acc[i] += ev[i].elapsed_time(ev[i + 1]) / REPS
+if rank == 0:
+    for name, t in zip(("splitters (torch + NCCL all_gather)", "partition + exchange (2 kernels)", "torch.empty x4",
+                        "local sort (dyn count)", "meta.cpu()"), acc):
+        print("world=%d  %-38s %8.1f us" % (world, name, t * 1e3))
+    print("world=%d  total %.1f us; received %d of capacity %d" % (world, sum(acc) * 1e3, int(host[-2]), cap))
+mg.disable_p2p()
+dist.destroy_process_group()
