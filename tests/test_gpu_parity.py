@@ -689,3 +689,71 @@ def test_batched_sort_sorting_networks_api(prim, batch, L, direction):
         assert (d >= 0).all() if direction else (d <= 0).all()
     assert (keys[gv] == gk).all()
     assert (np.sort(gv.reshape(batch, L), axis=1) == vals.reshape(batch, L)).all()
+
+
+# ============================================================ peer-window exchange (world = 1) and dyn-count sort
+def test_sort_with_device_side_count(prim):
+    """b200_sort_kv_dyn_async: the pair count is read on the device; capacity only sizes the launch."""
+    rng = np.random.default_rng(11)
+    cap = (1 << 18) + 4096
+    keys = rng.integers(0, 1 << 32, cap, dtype=np.uint64).astype(np.uint32)
+    vals = np.arange(cap, dtype=np.uint32)
+    sk, sv = dev(keys.view(np.int32)), dev(vals.view(np.int32))
+    for n in (0, 1, 8191, 8192, 100000, cap):
+        for direction in (1, 0):
+            dk, dv, bk, bv = (torch.full((cap,), -7, dtype=torch.int32, device="cuda") for _ in range(4))
+            d_n = torch.tensor([n, 0], dtype=torch.int32, device="cuda")
+            prim.sort_kv_dyn(dk, dv, bk, bv, sk, sv, cap, d_n, direction)
+            wk, wv = oracle.stable_sort_kv(keys[:n], vals[:n], direction)
+            assert (dk[:n].cpu().numpy().view(np.uint32) == wk).all(), (n, direction)
+            assert (dv[:n].cpu().numpy().view(np.uint32) == wv).all(), (n, direction)
+            assert bool((dk[n:] == -7).all()), "nothing beyond the counted pairs may be written"
+
+
+def test_peer_window_entry_points_world_1(prim):
+    """The fused compute + exchange kernels with a one-rank window set: same results as the plain kernels
+    (the 2/4/8-GPU case is tests/multi_gpu_check.py)."""
+    h = prim.p2p_window_create()
+    prim.p2p_connect(0, 1, [h])
+    try:
+        assert prim.p2p_world() == 1
+        rng = np.random.default_rng(5)
+        pay = dev(rng.integers(0, 1 << 31, 24, dtype=np.int64).astype(np.int32))
+        got = torch.empty(24, dtype=torch.int32, device="cuda")
+        for _ in range(3):
+            prim.p2p_allgather(pay, 96, got)
+        assert bool((got == pay).all())
+        # histogram -> all-reduce
+        data = rng.integers(0, 256, (1 << 22) + 48, dtype=np.uint8)
+        o256 = torch.empty(256, dtype=torch.int32, device="cuda")
+        o64 = torch.empty(64, dtype=torch.int32, device="cuda")
+        for _ in range(2):
+            prim.histogram_fused_allreduce(o256, o64, dev(data), data.size)
+            assert (o256.cpu().numpy().view(np.uint32) == oracle.histogram256(data)).all()
+            assert (o64.cpu().numpy().view(np.uint32) == oracle.histogram64(data)).all()
+        # reduce -> exchange -> rank-order sum (two slots: int then float)
+        xi = rng.integers(-2**31, 2**31, 1 << 20, dtype=np.int64).astype(np.int32)
+        xf = rng.random(1 << 20, dtype=np.float32)
+        slots = torch.zeros(2, dtype=torch.float64, device="cuda")
+        gathered = torch.zeros(2, dtype=torch.float64, device="cuda")
+        sums = torch.zeros(2, dtype=torch.float64, device="cuda")
+        prim.reduce_partial(dev(xi), xi.size, slots[0:1])
+        prim.reduce_partial_exchange(dev(xf), xf.size, slots, 1, 2, gathered, sums)
+        s = sums.cpu().numpy()
+        assert int(s[0]) == oracle.reduce(xi)
+        want = oracle.reduce(xf)
+        assert abs(float(s[1]) - want) <= FP32_RTOL * abs(want)
+        assert (gathered.cpu().numpy() == s).all()
+        # scan total -> carry (rank 0: no lower ranks)
+        src = rng.integers(0, 1 << 32, 1 << 20, dtype=np.uint64).astype(np.uint32)
+        carry = torch.full((1,), 99, dtype=torch.int32, device="cuda")
+        work = torch.zeros(18, dtype=torch.float64, device="cuda")
+        prim.scan_total_exchange(carry, dev(src.view(np.int32)), src.size, work)
+        assert int(carry.item()) == 0
+        total = int(work[0].item()) & 0xFFFFFFFF
+        assert total == int(src.sum(dtype=np.uint64) & 0xFFFFFFFF)
+        torch.cuda.synchronize()
+        assert prim.p2p_errors() == 0
+    finally:
+        prim.p2p_disconnect()
+    assert prim.p2p_world() == 0
