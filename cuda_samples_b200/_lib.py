@@ -32,6 +32,8 @@ SIGNATURES = {
     "b200_scalar_prod_async": (ci, [vp, vp, vp, ci, ci, vp]),
     "b200_scan_exclusive_async": (ci, [vp, vp, sz, sz, vp, vp]),
     "b200_scan_total_async": (ci, [vp, vp, sz, vp]),
+    "b200_scan_inclusive_async": (ci, [vp, vp, sz, sz, vp, vp]),
+    "b200_compact_positive_async": (ci, [vp, vp, vp, sz, vp]),
     "b200_sort_kv_async": (ci, [vp, vp, vp, vp, vp, vp, sz, u32, vp]),
     "b200_sort_kv_dyn_async": (ci, [vp, vp, vp, vp, vp, vp, sz, vp, u32, vp]),
     "b200_partition_kv_async": (ci, [vp, vp, vp, vp, sz, vp, u32, u32, vp, vp]),

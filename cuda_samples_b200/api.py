@@ -168,6 +168,17 @@ def scanExclusiveLarge(d_Dst, d_Src, batchSize, arrayLength, stream=None, d_carr
     return 512
 
 
+def scanInclusive(d_Dst, d_Src, batchSize, arrayLength, stream=None, d_carry=None):
+    """Inclusive +scan (the shfl_scan sample's result): d_Dst[j] = sum d_Src[0..j] per array, wrapping."""
+    check(lib.b200_scan_inclusive_async(_dptr(d_Dst), _dptr(d_Src), batchSize, arrayLength, _dptr(d_carry),
+                                        _stream(stream)), "scanInclusive")
+
+
+def filter_arr(dst, nres, src, n, stream=None):
+    """warpAggregatedAtomicsCG's filter_arr(dst, nres, src, n): keeps src[i] > 0 -- here in input order."""
+    check(lib.b200_compact_positive_async(_dptr(dst), _dptr(nres), _dptr(src), n, _stream(stream)), "filter_arr")
+
+
 def scan_total(d_total, d_Src, n, stream=None):
     check(lib.b200_scan_total_async(_dptr(d_total), _dptr(d_Src), n, _stream(stream)), "scan_total")
 

@@ -39,6 +39,7 @@ struct ScanParams {
     unsigned        packed;     // 1: power-of-two L < tile, tiles cover whole arrays back to back
     const unsigned *carry;      // nullable: seed of element 0 of every array
     unsigned        backoff_ns; // pause between unsuccessful look-back polls
+    unsigned        incl;       // 0: exclusive; 0xffffffff: inclusive (every element also receives itself)
 };
 
 __device__ __forceinline__ unsigned long long make_desc(unsigned epoch, unsigned state, unsigned value)
@@ -282,6 +283,10 @@ __global__ void __launch_bounds__(kScanThreads, 3)
         o.y = e0 + v[k].x;
         o.z = o.y + v[k].y;
         o.w = o.z + v[k].z;
+        o.x += v[k].x & p.incl; // inclusive scan (shfl_scan sample): element i also receives src[i]
+        o.y += v[k].y & p.incl;
+        o.z += v[k].z & p.incl;
+        o.w += v[k].w & p.incl;
         if (fast) {
             st_stream_u4(dst + off + ebase[k], o);
         }
@@ -632,6 +637,10 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
             o.y = e0 + v[r].x;
             o.z = o.y + v[r].y;
             o.w = o.z + v[r].z;
+            o.x += v[r].x & p.incl;
+            o.y += v[r].y & p.incl;
+            o.z += v[r].z & p.incl;
+            o.w += v[r].w & p.incl;
             if (ebase[r] < count)
                 st_stream_u4(out + ebase[r], o);
         }
@@ -646,8 +655,8 @@ static int  g_scan_backoff_ns = 100;
 
 using namespace b200;
 
-extern "C" int b200_scan_exclusive_async(uint32_t *d_dst, const uint32_t *d_src, size_t batch, size_t L,
-                                         const uint32_t *d_carry, b200_stream_t stream_)
+static int scan_impl(uint32_t *d_dst, const uint32_t *d_src, size_t batch, size_t L, const uint32_t *d_carry,
+                     bool inclusive, b200_stream_t stream_)
 {
     cudaStream_t stream = (cudaStream_t)stream_;
     if (batch == 0 || L == 0)
@@ -661,6 +670,7 @@ extern "C" int b200_scan_exclusive_async(uint32_t *d_dst, const uint32_t *d_src,
     p.L     = L;
     p.carry = d_carry;
     p.backoff_ns = (unsigned)g_scan_backoff_ns;
+    p.incl       = inclusive ? 0xffffffffu : 0u;
     bool large;
     if (L >= kScanTile || !is_pow2(L) || L < 4) {
         // tile-aligned arrays (look-back inside an array when it spans several tiles)
@@ -739,6 +749,21 @@ extern "C" int b200_scan_exclusive_async(uint32_t *d_dst, const uint32_t *d_src,
     count_launch();
     B200_TRY(cudaGetLastError());
     return 0;
+}
+
+extern "C" int b200_scan_exclusive_async(uint32_t *d_dst, const uint32_t *d_src, size_t batch, size_t L,
+                                         const uint32_t *d_carry, b200_stream_t stream)
+{
+    return scan_impl(d_dst, d_src, batch, L, d_carry, false, stream);
+}
+
+// Inclusive +scan (dst[j] = sum of src[0..j], wrapping): what the shfl_scan sample computes with three launches
+// (shfl_scan_test x2 + uniform_add, Samples/2_Concepts_and_Techniques/shfl_scan/shfl_scan.cu:55-147, host
+// sequence :275-277, gold :157-161) -- here the same single-pass kernels with one extra add per element.
+extern "C" int b200_scan_inclusive_async(uint32_t *d_dst, const uint32_t *d_src, size_t batch, size_t L,
+                                         const uint32_t *d_carry, b200_stream_t stream)
+{
+    return scan_impl(d_dst, d_src, batch, L, d_carry, true, stream);
 }
 
 // tuning knob for tests / bench (not part of the stable ABI): 0 = register-staged chained scan only

@@ -74,6 +74,16 @@ int b200_scalar_prod_async(float *d_C, const float *d_A, const float *d_B, int v
 int b200_scan_exclusive_async(uint32_t *d_dst, const uint32_t *d_src, size_t batchSize, size_t arrayLength,
                               const uint32_t *d_carry, b200_stream_t stream);
 int b200_scan_total_async(uint32_t *d_total, const uint32_t *d_src, size_t n, b200_stream_t stream);
+/* scan siblings.  Inclusive scan: dst[j] = sum src[0..j] -- what the shfl_scan sample computes
+ * with shfl_scan_test x2 + uniform_add (shfl_scan.cu:55-147, host sequence :275-277, gold :157-161); same
+ * single-pass kernels, same arguments as b200_scan_exclusive_async. */
+int b200_scan_inclusive_async(uint32_t *d_dst, const uint32_t *d_src, size_t batchSize, size_t arrayLength,
+                              const uint32_t *d_carry, b200_stream_t stream);
+/* stream compaction: d_dst[0 .. *d_count) = the elements of d_src[0 .. n) that are > 0, IN INPUT ORDER (filter_arr of
+ * warpAggregatedAtomicsCG.cu:59-68 keeps the same set in arbitrary order; its host gold :287-292 is ordered).
+ * One single-pass chained-scan kernel; 4 B read per element + 4 B written per kept element.  n < 2^30. */
+int b200_compact_positive_async(int32_t *d_dst, int32_t *d_count, const int32_t *d_src, size_t n,
+                                b200_stream_t stream);
 
 /* sort: replaces mergeSort() (mergeSort.cu:471-537): STABLE key-value sort, sortDir != 0 ascending,
  * == 0 descending, ties keep source order.  Result in dst, buf is scratch, src is left untouched.

@@ -58,6 +58,9 @@ def _load():
     lib.oracle_fill_values.argtypes = [c_void, u64]
     lib.oracle_fill_sample_input.argtypes = [c_void, u64, u32, ctypes.c_int]
     lib.oracle_generate.argtypes = [c_void, u64, u64, u64, ctypes.c_int, u32]
+    lib.oracle_scan_inclusive.argtypes = [c_void, c_void, u64]
+    lib.oracle_filter_positive.argtypes = [c_void, c_void, u64]
+    lib.oracle_filter_positive.restype = u64
     lib.oracle_fnv1a64.argtypes = [c_void, u64]
     lib.oracle_fnv1a64.restype = u64
     return lib
@@ -87,6 +90,22 @@ def scan_exclusive(src, batch, length, carry=0):
     dst = np.empty_like(src)
     _lib.oracle_scan_exclusive(_ptr(dst), _ptr(src), batch, length, carry)
     return dst
+
+
+def scan_inclusive(src):
+    """Running sum of a u32/i32 array (shfl_scan.cu:157-161 CPUverify), wrapping."""
+    src = np.ascontiguousarray(src).view(np.uint32)
+    dst = np.empty_like(src)
+    _lib.oracle_scan_inclusive(_ptr(dst), _ptr(src), src.size)
+    return dst
+
+
+def filter_positive(src):
+    """Elements > 0 in input order (warpAggregatedAtomicsCG.cu:287-292 host loop)."""
+    src = np.ascontiguousarray(src, dtype=np.int32)
+    dst = np.empty_like(src)
+    n = _lib.oracle_filter_positive(_ptr(dst), _ptr(src), src.size)
+    return dst[:n].copy()
 
 
 def reduce(data):

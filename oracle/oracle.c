@@ -449,6 +449,28 @@ void oracle_generate(void *out, uint64_t first, uint64_t n, uint64_t seed, int k
 }
 
 /* FNV-1a 64 over bytes (the hash the SURVEY.md 8c known answers are quoted in). */
+/* shfl_scan sample, CPUverify (Samples/2_Concepts_and_Techniques/shfl_scan/shfl_scan.cu:157-161): the gold is the
+ * running sum h_data[i + 1] = h_data[i] + h_data[i + 1], i.e. an INCLUSIVE scan (int arithmetic, wraps). */
+void oracle_scan_inclusive(uint32_t *dst, const uint32_t *src, uint64_t n)
+{
+    uint32_t run = 0;
+    for (uint64_t i = 0; i < n; i++) {
+        run += src[i];
+        dst[i] = run;
+    }
+}
+
+/* warpAggregatedAtomicsCG sample, host loop of main() (Samples/3_CUDA_Features/warpAggregatedAtomicsCG/
+ * warpAggregatedAtomicsCG.cu:287-292): if (data_to_filter[i] > 0) host_filtered_data[host_flt_count++] = ... */
+uint64_t oracle_filter_positive(int32_t *dst, const int32_t *src, uint64_t n)
+{
+    uint64_t count = 0;
+    for (uint64_t i = 0; i < n; i++)
+        if (src[i] > 0)
+            dst[count++] = src[i];
+    return count;
+}
+
 uint64_t oracle_fnv1a64(const void *data, uint64_t nbytes)
 {
     const uint8_t *p = (const uint8_t *)data;

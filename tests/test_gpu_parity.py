@@ -757,3 +757,50 @@ def test_peer_window_entry_points_world_1(prim):
     finally:
         prim.p2p_disconnect()
     assert prim.p2p_world() == 0
+
+
+# ===================================================================== scan siblings
+@pytest.mark.parametrize("n", [1, 5, 1024, 8191, 8192, 65536, (1 << 20) + 3, 1 << 24])
+def test_scan_inclusive_matches_shfl_scan_gold(prim, n):
+    rng = np.random.default_rng(n)
+    src = rng.integers(0, 1 << 32, n, dtype=np.uint64).astype(np.uint32)
+    s = dev(src.view(np.int32))
+    d = torch.empty_like(s)
+    prim.scanInclusive(d, s, 1, n)
+    assert (d.cpu().numpy().view(np.uint32) == oracle.scan_inclusive(src)).all()
+    if n == 65536:  # the sample's own input: all ones -> 1..n (shfl_scan.cu:246-248)
+        ones = torch.ones(n, dtype=torch.int32, device="cuda")
+        prim.scanInclusive(ones, ones, 1, n)  # in place like the sample
+        assert (ones.cpu().numpy() == np.arange(1, n + 1)).all()
+
+
+def test_scan_inclusive_batched(prim):
+    rng = np.random.default_rng(3)
+    for batch, L in ((4096, 256), (64, 16384), (3, 100000)):
+        src = rng.integers(0, 1 << 32, batch * L, dtype=np.uint64).astype(np.uint32)
+        d = torch.empty(batch * L, dtype=torch.int32, device="cuda")
+        prim.scanInclusive(d, dev(src.view(np.int32)), batch, L)
+        want = np.concatenate([oracle.scan_inclusive(src[a * L:(a + 1) * L]) for a in range(batch)])
+        assert (d.cpu().numpy().view(np.uint32) == want).all(), (batch, L)
+
+
+@pytest.mark.parametrize("n", [0, 1, 31, 8192, 8193, 100001, 1 << 22, (1 << 24) + 5])
+@pytest.mark.parametrize("kind", ["sample", "signed", "none", "all"])
+def test_compaction_matches_host_filter(prim, n, kind):
+    rng = np.random.default_rng(n + len(kind))
+    if kind == "sample":      # warpAggregatedAtomicsCG.cu:255-257: rand() % 5
+        src = rng.integers(0, 5, n, dtype=np.int64).astype(np.int32)
+    elif kind == "signed":
+        src = rng.integers(-2**31, 2**31, n, dtype=np.int64).astype(np.int32)
+    elif kind == "none":
+        src = -rng.integers(0, 100, n, dtype=np.int64).astype(np.int32)
+    else:
+        src = rng.integers(1, 100, n, dtype=np.int64).astype(np.int32)
+    s = dev(src) if n else torch.empty(0, dtype=torch.int32, device="cuda")
+    dst = torch.full((max(n, 1),), -99, dtype=torch.int32, device="cuda")
+    cnt = torch.full((1,), -1, dtype=torch.int32, device="cuda")
+    prim.filter_arr(dst, cnt, s, n)
+    want = oracle.filter_positive(src)
+    assert int(cnt.item()) == want.size
+    assert (dst[:want.size].cpu().numpy() == want).all()
+    assert bool((dst[want.size:] == -99).all())

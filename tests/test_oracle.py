@@ -180,3 +180,16 @@ def test_scalar_prod_restatement_equals_reference_gold():
         a = rng.random(vn * en, dtype=np.float32)
         b = (rng.random(vn * en, dtype=np.float32) - 0.5).astype(np.float32)
         assert (oracle.scalar_prod(a, b, vn, en) == oracle.ref.scalar_prod(a, b, vn, en)).all()
+
+
+def test_scan_siblings_oracle():
+    """Inclusive scan (shfl_scan CPUverify) and the ordered filter (warpAggregatedAtomicsCG host loop)."""
+    import oracle
+    rng = np.random.default_rng(1)
+    src = rng.integers(0, 1 << 32, 10007, dtype=np.uint64).astype(np.uint32)
+    assert (oracle.scan_inclusive(src) == np.cumsum(src.astype(np.uint64)).astype(np.uint32)).all()
+    ex = oracle.scan_exclusive(src, 1, src.size)
+    assert (oracle.scan_inclusive(src) == ex + src).all()
+    x = rng.integers(-3, 4, 5000, dtype=np.int64).astype(np.int32)
+    assert (oracle.filter_positive(x) == x[x > 0]).all()
+    assert oracle.filter_positive(np.zeros(0, dtype=np.int32)).size == 0
