@@ -249,6 +249,20 @@ def primitives_table(torch, dist, prim, mg, rank, world, peak, barrier, p2p=Fals
         def step_scan_short():
             prim.scanExclusiveShort(dst, src, n // 1024, 1024)
         record("scanExclusiveShort_L1024_2^28", time_steps(torch, step_scan_short, 20, 4) / 20, 8 * N_ELEMS)
+        # scan siblings: inclusive scan (shfl_scan) and ordered stream compaction (filter_arr)
+
+        def step_scan_incl():
+            prim.scanInclusive(dst, src, 1, n)
+        record("scanInclusive_2^28", time_steps(torch, step_scan_incl, 20, 4) / 20, 8 * N_ELEMS)
+        prim.generate(src, "key_mod", 0, n, 7, 5)  # the sample's rand() % 5: 80 % of the elements are kept
+        cnt = torch.zeros(1, dtype=torch.int32, device="cuda")
+
+        def step_compact():
+            prim.filter_arr(dst, cnt, src, n)
+        t_c = time_steps(torch, step_compact, 20, 4) / 20
+        kept = int(cnt.item())
+        record("filter_arr_compaction_2^28", t_c, 4 * N_ELEMS + 4 * kept,
+               {"kept": kept, "note": "4 B read per element + 4 B written per kept element, output in input order"})
     del src, dst
     # --- reduction sibling: batched dot products, 4096 vectors x 65536 floats (2 GiB read)
     if world == 1:

@@ -40,6 +40,7 @@ struct ScanParams {
     const unsigned *carry;      // nullable: seed of element 0 of every array
     unsigned        backoff_ns; // pause between unsuccessful look-back polls
     unsigned        incl;       // 0: exclusive; 0xffffffff: inclusive (every element also receives itself)
+    int            *count_out;  // compaction mode of the TMA kernel: number of kept elements
 };
 
 __device__ __forceinline__ unsigned long long make_desc(unsigned epoch, unsigned state, unsigned value)
@@ -392,7 +393,9 @@ __device__ __forceinline__ void mbar_arrive(uint64_t *bar)
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
-template <int kTmaRows, int kTmaStages, int kTmaAhead>
+// kCompact: the same pipeline as a stable stream compaction (compact.cu): the scanned quantity is the flag
+// (int)x > 0, and instead of the prefixes the kept elements themselves are stored at their prefix positions.
+template <int kTmaRows, int kTmaStages, int kTmaAhead, bool kCompact = false>
 __global__ void __launch_bounds__(kTmaThreads, 1)
     scan_tma_kernel(unsigned *dst, const unsigned *src, const ScanParams p, unsigned long long *state,
                     unsigned long long *desc)
@@ -564,8 +567,12 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
             for (int r = 0; r < kTmaRows; r++) {
                 const unsigned e = warp * (kTmaRows * 128) + r * 128 + lane * 4;
                 uint4          v = *reinterpret_cast<const uint4 *>(&S.buf[s][e]);
-                if (e < count) // ragged last tile of an array (count is a multiple of 4 here)
-                    sum += (v.x + v.y) + (v.z + v.w);
+                if (e < count) { // ragged last tile of an array (count is a multiple of 4 here)
+                    if (kCompact)
+                        sum += ((int)v.x > 0) + ((int)v.y > 0) + ((int)v.z > 0) + ((int)v.w > 0);
+                    else
+                        sum += (v.x + v.y) + (v.z + v.w);
+                }
             }
             sum = __reduce_add_sync(0xffffffffu, sum);
             if (lane == 0) {
@@ -600,7 +607,10 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
             v[r]     = *reinterpret_cast<const uint4 *>(&S.buf[s][ebase[r]]);
             if (ebase[r] >= count)
                 v[r] = make_uint4(0, 0, 0, 0);
-            tot[r] = (v[r].x + v[r].y) + (v[r].z + v[r].w);
+            if (kCompact)
+                tot[r] = ((int)v[r].x > 0) + ((int)v[r].y > 0) + ((int)v[r].z > 0) + ((int)v[r].w > 0);
+            else
+                tot[r] = (v[r].x + v[r].y) + (v[r].z + v[r].w);
             inc[r] = tot[r];
         }
 #pragma unroll
@@ -632,6 +642,18 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
         for (int r = 0; r < kTmaRows; r++) {
             const unsigned e0 = run + (inc[r] - tot[r]);
             run += __shfl_sync(0xffffffffu, inc[r], 31);
+            if (kCompact) { // zeros stand in for elements beyond `count`: never kept
+                unsigned pos = e0;
+                if ((int)v[r].x > 0)
+                    dst[pos++] = v[r].x;
+                if ((int)v[r].y > 0)
+                    dst[pos++] = v[r].y;
+                if ((int)v[r].z > 0)
+                    dst[pos++] = v[r].z;
+                if ((int)v[r].w > 0)
+                    dst[pos++] = v[r].w;
+                continue;
+            }
             uint4 o;
             o.x = e0;
             o.y = e0 + v[r].x;
@@ -644,6 +666,8 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
             if (ebase[r] < count)
                 st_stream_u4(out + ebase[r], o);
         }
+        if (kCompact && tile_b == p.num_tiles - 1 && warp == kScanWarps - 1 && lane == 0)
+            *p.count_out = (int)run; // prefix + everything kept in the last tile
     }
 }
 
@@ -671,6 +695,7 @@ static int scan_impl(uint32_t *d_dst, const uint32_t *d_src, size_t batch, size_
     p.carry = d_carry;
     p.backoff_ns = (unsigned)g_scan_backoff_ns;
     p.incl       = inclusive ? 0xffffffffu : 0u;
+    p.count_out  = nullptr;
     bool large;
     if (L >= kScanTile || !is_pow2(L) || L < 4) {
         // tile-aligned arrays (look-back inside an array when it spans several tiles)
@@ -764,6 +789,54 @@ extern "C" int b200_scan_inclusive_async(uint32_t *d_dst, const uint32_t *d_src,
                                          const uint32_t *d_carry, b200_stream_t stream)
 {
     return scan_impl(d_dst, d_src, batch, L, d_carry, true, stream);
+}
+
+// Stream compaction on the TMA-staged chained-scan pipeline (called by compact.cu for long, 16-byte aligned
+// inputs with n % 4 == 0; everything else takes compact_kernel).  Returns cudaErrorNotSupported when the shape
+// does not qualify.
+int compact_tma(int32_t *d_dst, int32_t *d_count, const int32_t *d_src, size_t n, cudaStream_t stream)
+{
+    constexpr unsigned tile = kScanThreads * 5 * 4;
+    if (n < 4 * (size_t)tile || (n & 3) || (((uintptr_t)d_src) & 15) || !g_scan_use_tma)
+        return (int)cudaErrorNotSupported;
+    int        st = 0;
+    DeviceCtx *c  = ctx(&st);
+    if (!c)
+        return st;
+    ScanParams p;
+    p.total      = n;
+    p.L          = n;
+    p.carry      = nullptr;
+    p.backoff_ns = (unsigned)g_scan_backoff_ns;
+    p.incl       = 0;
+    p.count_out  = d_count;
+    p.lane_seg   = 32;
+    p.rows_seg   = kScanRows;
+    p.warps_seg  = kScanWarps;
+    p.packed     = 0;
+    const size_t tpa = (n + tile - 1) / tile;
+    if (tpa > 0xfffffff0ull)
+        return (int)cudaErrorInvalidValue;
+    p.tpa       = (unsigned)tpa;
+    p.num_tiles = (unsigned)tpa;
+    const size_t nd = tpa + (tpa + 31) / 32;
+    B200_TRY((cudaError_t)ensure(c->scan, 16 + 8 * nd, stream));
+    auto *st64 = reinterpret_cast<unsigned long long *>(c->scan.ptr);
+    auto *desc = reinterpret_cast<unsigned long long *>(reinterpret_cast<char *>(c->scan.ptr) + 16);
+    unsigned grid = (unsigned)c->num_sms;
+    if (grid > p.num_tiles)
+        grid = p.num_tiles;
+    static bool prepared = false;
+    if (!prepared) {
+        B200_TRY(cudaFuncSetAttribute(scan_tma_kernel<5, 5, 3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)sizeof(ScanTmaSmem<5, 5>)));
+        prepared = true;
+    }
+    scan_tma_kernel<5, 5, 3, true><<<grid, kTmaThreads, sizeof(ScanTmaSmem<5, 5>), stream>>>(
+        reinterpret_cast<unsigned *>(d_dst), reinterpret_cast<const unsigned *>(d_src), p, st64, desc);
+    count_launch();
+    B200_TRY(cudaGetLastError());
+    return 0;
 }
 
 // tuning knob for tests / bench (not part of the stable ABI): 0 = register-staged chained scan only

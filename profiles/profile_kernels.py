@@ -46,6 +46,10 @@ if which in ("all", "scan"):
     for _ in range(REPS):
         prim.scanExclusiveLarge(dst, src, 1, N)
         prim.scanExclusiveShort(dst, src, N // 1024, 1024)
+    prim.generate(src, "key_mod", 0, N, 7, 5)
+    cnt = torch.zeros(1, dtype=torch.int32, device="cuda")
+    for _ in range(REPS):
+        prim.filter_arr(dst, cnt, src, N)
     torch.cuda.synchronize()
     del src, dst
 
