@@ -34,6 +34,7 @@ SIGNATURES = {
     "b200_scan_total_async": (ci, [vp, vp, sz, vp]),
     "b200_scan_inclusive_async": (ci, [vp, vp, sz, sz, vp, vp]),
     "b200_compact_positive_async": (ci, [vp, vp, vp, sz, vp]),
+    "b200_integral_image_u8_async": (ci, [vp, vp, sz, sz, vp]),
     "b200_sort_kv_async": (ci, [vp, vp, vp, vp, vp, vp, sz, u32, vp]),
     "b200_sort_kv_dyn_async": (ci, [vp, vp, vp, vp, vp, vp, sz, vp, u32, vp]),
     "b200_partition_kv_async": (ci, [vp, vp, vp, vp, sz, vp, u32, u32, vp, vp]),

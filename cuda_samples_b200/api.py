@@ -179,6 +179,12 @@ def filter_arr(dst, nres, src, n, stream=None):
     check(lib.b200_compact_positive_async(_dptr(dst), _dptr(nres), _dptr(src), n, _stream(stream)), "filter_arr")
 
 
+def integral_image(d_out, d_img, width, height, stream=None):
+    """Summed-area table of a u8 image (shfl_scan sample, shuffle_integral_image_test): d_out u32[height*width]."""
+    check(lib.b200_integral_image_u8_async(_dptr(d_out), _dptr(d_img), width, height, _stream(stream)),
+          "integral_image")
+
+
 def scan_total(d_total, d_Src, n, stream=None):
     check(lib.b200_scan_total_async(_dptr(d_total), _dptr(d_Src), n, _stream(stream)), "scan_total")
 

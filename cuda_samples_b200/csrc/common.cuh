@@ -50,6 +50,7 @@ struct DeviceCtx {
     Scratch hist;         // accumulators + ticket
     Scratch scan;         // state + tile descriptors
     Scratch sort;         // digit histograms + descriptors
+    Scratch image;        // integral image: band / block carries
     Scratch stage[2];     // device staging chunks of the host-buffer entry points
     cudaStream_t copy_stream[2] = {nullptr, nullptr}; // H2D / D2H engines of the host-buffer entry points
     cudaStream_t compute_stream = nullptr;

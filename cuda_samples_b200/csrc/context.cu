@@ -122,6 +122,7 @@ extern "C" int b200_release_scratch(void)
     release(c->hist);
     release(c->scan);
     release(c->sort);
+    release(c->image);
     release(c->stage[0]);
     release(c->stage[1]);
     return 0;

@@ -84,6 +84,12 @@ int b200_scan_inclusive_async(uint32_t *d_dst, const uint32_t *d_src, size_t bat
  * One single-pass chained-scan kernel; 4 B read per element + 4 B written per kept element.  n < 2^30. */
 int b200_compact_positive_async(int32_t *d_dst, int32_t *d_count, const int32_t *d_src, size_t n,
                                 b200_stream_t stream);
+/* Integral image (summed-area table) of an 8-bit image, the shfl_scan sample's second test (shfl_intimage_rows +
+ * shfl_vertical_shfl, shfl_integral_image.cuh:168-320, host sequence shfl_scan.cu:308-381):
+ * d_out[r * width + c] = sum of d_img[r' * width + c'], r' <= r, c' <= c (u32, wraps).  Rows are `width` bytes
+ * apart.  Any width, height >= 0 with width * height < 2^32; every output pixel is written once (5 B per pixel). */
+int b200_integral_image_u8_async(uint32_t *d_out, const uint8_t *d_img, size_t width, size_t height,
+                                 b200_stream_t stream);
 
 /* sort: replaces mergeSort() (mergeSort.cu:471-537): STABLE key-value sort, sortDir != 0 ascending,
  * == 0 descending, ties keep source order.  Result in dst, buf is scratch, src is left untouched.

@@ -61,6 +61,7 @@ def _load():
     lib.oracle_scan_inclusive.argtypes = [c_void, c_void, u64]
     lib.oracle_filter_positive.argtypes = [c_void, c_void, u64]
     lib.oracle_filter_positive.restype = u64
+    lib.oracle_integral_image_u8.argtypes = [c_void, c_void, u32, u32]
     lib.oracle_fnv1a64.argtypes = [c_void, u64]
     lib.oracle_fnv1a64.restype = u64
     return lib
@@ -106,6 +107,16 @@ def filter_positive(src):
     dst = np.empty_like(src)
     n = _lib.oracle_filter_positive(_ptr(dst), _ptr(src), src.size)
     return dst[:n].copy()
+
+
+def integral_image(img):
+    """Summed-area table of a 2-D u8 image (shfl_scan.cu:308-381 restated), u32, wrapping."""
+    img = np.ascontiguousarray(img, dtype=np.uint8)
+    h, w = img.shape
+    dst = np.empty((h, w), np.uint32)
+    if h and w:
+        _lib.oracle_integral_image_u8(_ptr(dst), _ptr(img), w, h)
+    return dst
 
 
 def reduce(data):

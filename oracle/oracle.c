@@ -471,6 +471,24 @@ uint64_t oracle_filter_positive(int32_t *dst, const int32_t *src, uint64_t n)
     return count;
 }
 
+/* shfl_scan sample, integral image test (Samples/2_Concepts_and_Techniques/shfl_scan/shfl_scan.cu:308-381): the
+ * first kernel leaves the prefix sums of every scanline (what verifyDataRowSums checks, :193-205: gold = i + 1 on
+ * the all-ones image), the second turns every column into its running sum in place (shfl_integral_image.cuh:268-320),
+ * and the corner must equal w * h (:372-381).  Restated as those two steps, u32 arithmetic. */
+void oracle_integral_image_u8(uint32_t *dst, const uint8_t *img, uint32_t w, uint32_t h)
+{
+    for (uint64_t r = 0; r < h; r++) {
+        uint32_t run = 0;
+        for (uint64_t c = 0; c < w; c++) {
+            run += img[r * w + c];
+            dst[r * w + c] = run;
+        }
+    }
+    for (uint64_t r = 1; r < h; r++)
+        for (uint64_t c = 0; c < w; c++)
+            dst[r * w + c] += dst[(r - 1) * w + c];
+}
+
 uint64_t oracle_fnv1a64(const void *data, uint64_t nbytes)
 {
     const uint8_t *p = (const uint8_t *)data;

@@ -804,3 +804,42 @@ def test_compaction_matches_host_filter(prim, n, kind):
     assert int(cnt.item()) == want.size
     assert (dst[:want.size].cpu().numpy() == want).all()
     assert bool((dst[want.size:] == -99).all())
+
+
+@pytest.mark.parametrize("shape", [(1080, 1920), (1, 1), (1, 4), (7, 128), (33, 132), (64, 4096), (100, 1000),
+                                   (257, 515), (31, 3), (1000, 130), (2049, 2052), (4096, 8192)])
+def test_integral_image_matches_oracle(prim, shape):
+    h, w = shape
+    rng = np.random.default_rng(h * 7919 + w)
+    img = rng.integers(0, 256, (h, w), dtype=np.uint8)
+    if shape == (1080, 1920):  # the sample's input: every byte 1 (shfl_scan.cu:333), corner = w*h (:372-381)
+        img[:] = 1
+    d_img = torch.from_numpy(img).cuda()
+    out = torch.full((h * w,), -1, dtype=torch.int32, device="cuda")
+    prim.integral_image(out, d_img, w, h)
+    got = out.cpu().numpy().view(np.uint32).reshape(h, w)
+    assert (got == oracle.integral_image(img)).all()
+    if shape == (1080, 1920):
+        assert int(got[-1, -1]) == w * h and (got[0] == np.arange(1, w + 1)).all()
+
+
+@pytest.mark.parametrize("rows", [8, 16, 32])
+def test_integral_image_band_heights_and_wrap(prim, rows, monkeypatch):
+    """All band heights give the same table; 255-valued 8192 x 4100 image wraps u32 exactly like the oracle."""
+    import ctypes
+    from cuda_samples_b200 import _lib
+    knob = ctypes.c_int.in_dll(_lib.lib, "g_ii_rows")
+    knob.value = rows
+    try:
+        h, w = 4100, 8192
+        img = np.full((h, w), 255, np.uint8)
+        img[::3, ::5] = 17
+        out = torch.empty(h * w, dtype=torch.int32, device="cuda")
+        prim.integral_image(out, torch.from_numpy(img).cuda(), w, h)
+        assert (out.cpu().numpy().view(np.uint32).reshape(h, w) == oracle.integral_image(img)).all()
+        img = np.random.default_rng(rows).integers(0, 256, (45, 77), dtype=np.uint8)   # unaligned variant
+        out = torch.empty(45 * 77, dtype=torch.int32, device="cuda")
+        prim.integral_image(out, torch.from_numpy(img).cuda(), 77, 45)
+        assert (out.cpu().numpy().view(np.uint32).reshape(45, 77) == oracle.integral_image(img)).all()
+    finally:
+        knob.value = 0

@@ -193,3 +193,19 @@ def test_scan_siblings_oracle():
     x = rng.integers(-3, 4, 5000, dtype=np.int64).astype(np.int32)
     assert (oracle.filter_positive(x) == x[x > 0]).all()
     assert oracle.filter_positive(np.zeros(0, dtype=np.int32)).size == 0
+
+
+def test_integral_image_oracle_matches_the_samples_checks():
+    """shfl_scan's own acceptance checks on its own input (all-ones 1920x1080: row sums i+1, corner w*h,
+    shfl_scan.cu:193-205, :372-381) and numpy's double cumsum on random images."""
+    import oracle
+    w, h = 1920, 1080
+    out = oracle.integral_image(np.ones((h, w), np.uint8))
+    assert (out[0] == np.arange(1, w + 1)).all() and int(out[-1, -1]) == w * h
+    assert (out[:, 0] == np.arange(1, h + 1)).all()
+    rng = np.random.default_rng(7)
+    for hh, ww in ((1, 1), (3, 5), (37, 129), (200, 333)):
+        img = rng.integers(0, 256, (hh, ww), dtype=np.uint8)
+        want = np.cumsum(np.cumsum(img.astype(np.uint64), axis=1), axis=0).astype(np.uint32)
+        assert (oracle.integral_image(img) == want).all()
+    assert oracle.integral_image(np.zeros((0, 4), np.uint8)).size == 0
