@@ -32,6 +32,10 @@ SAMPLES = {
     # "next" row
     "sortingNetworks": ("2_Concepts_and_Techniques/sortingNetworks", ["main.cpp", "sortingNetworks_validate.cpp"],
                         ["bitonicSort.cu", "oddEvenMergeSort.cu"]),
+    # "next" row rank 4: the kernels live in the driver's own translation unit, so there is no drop-in link;
+    # only the reference build, for its own timings on the same box
+    "shfl_scan": ("2_Concepts_and_Techniques/shfl_scan", [], ["shfl_scan.cu"]),
+    "warpAggregatedAtomicsCG": ("3_CUDA_Features/warpAggregatedAtomicsCG", [], ["warpAggregatedAtomicsCG.cu"]),
 }
 
 
@@ -78,7 +82,8 @@ def build_all(which=None):
     for name in SAMPLES:
         if which and name not in which:
             continue
-        built.append(build_dropin(name))
+        if SAMPLES[name][1]:
+            built.append(build_dropin(name))
         built.append(build_reference_gpu(name))
     return built
 

@@ -20,6 +20,8 @@ RUNS = [
     ("scan", []),
     ("mergeSort", []),
     ("sortingNetworks", []),
+    ("shfl_scan", []),
+    ("warpAggregatedAtomicsCG", []),
 ]
 
 
@@ -36,7 +38,7 @@ def main(out_dir):
             with open(os.path.join(out_dir, "baseline_%s.log" % tag), "w") as f:
                 f.write(r.stdout + "\n--- stderr ---\n" + r.stderr)
             lines = [l.strip() for l in r.stdout.splitlines()
-                     if re.search(r"Throughput|Time:|stable|Test passed|Test failed|CPU result|GPU result", l)]
+                     if re.search(r"Throughput|Time:|Time \(|MegaElements|CheckSum|stable|Test passed|Test failed|CPU result|GPU result", l)]
             summary.append({"run": tag, "exit_code": r.returncode, "lines": lines})
             print(tag, "exit", r.returncode)
             for l in lines:

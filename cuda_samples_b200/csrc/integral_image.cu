@@ -12,8 +12,8 @@
 //                 the horizontal prefix of a row is one warp scan -- no shared memory, no CTA barrier.
 //   ii_sums       reads the image once: per tile the column sums over the band (packed 16-bit SIMD adds) and the
 //                 row sums over the block (dp4a + redux.sync).
-//   ii_prefix     exclusive prefix of the column sums down the bands, exclusive prefix of the row sums along the
-//                 blocks (both matrices are 1/R resp. 1/128 of the image).
+//   ii_prefix     one launch, two roles: exclusive prefix of the column sums down the bands (matrix = 1/R of the
+//                 output) and exclusive prefix of the row sums along the blocks (1/128 of the output).
 //   scan          the library's own batched inclusive scan along each band row of the column carries: after it
 //                 carry[b][c] = out[first row of band b - 1][c], the full integral above the band.
 //   ii_write      per tile: acc(c) = carry[b][c]; for each row: 4-pixel prefix, warp scan (two rows per scan, 16
@@ -25,6 +25,10 @@
 namespace b200 {
 
 constexpr unsigned kIICols  = 128; // columns per tile
+#ifndef B200_II_BATCH
+#define B200_II_BATCH 4
+#endif
+constexpr unsigned kIIBatch = B200_II_BATCH; // rows loaded ahead per iteration of ii_write (even)
 constexpr unsigned kIIWarps = 8;   // warps per CTA (tiles are independent; the CTA is only a scheduling unit)
 
 struct IIParams {
@@ -75,43 +79,114 @@ __global__ void __launch_bounds__(kIIWarps * 32) ii_sums_kernel(const IIParams p
         make_uint4(lo & 0xffffu, hi & 0xffffu, lo >> 16, hi >> 16);
 }
 
-// blocks [0, wp/128): one thread per column, exclusive prefix down the bands; the rest: one thread per image row,
-// exclusive prefix along the blocks.  Both loops only chain adds; the loads are independent.
-__global__ void __launch_bounds__(128) ii_prefix_kernel(const IIParams p)
+// The same sums from 16-byte loads (rows 16-byte aligned): a warp covers R rows x 512 columns = four blocks, lane l
+// owns columns 16l..16l+15; the row sums of a block are a reduction over its 8 lanes.
+__global__ void __launch_bounds__(kIIWarps * 32) ii_sums16_kernel(const IIParams p)
 {
-    if (blockIdx.x < p.nblk) {
-        uint32_t *m   = p.colcarry + blockIdx.x * 128 + threadIdx.x;
-        unsigned  run = 0;
-        for (unsigned b0 = 0; b0 < p.nbands; b0 += 8) {
-            unsigned t[8];
+    const unsigned lane = lane_id();
+    const unsigned nsb  = (p.nblk + 3) / 4; // 512-column super blocks per band
+    const unsigned tile = blockIdx.x * kIIWarps + (threadIdx.x >> 5);
+    if (tile >= p.nbands * nsb)
+        return;
+    const unsigned b = tile / nsb, sb = tile - b * nsb;
+    const unsigned r0 = b * p.R, rows = min(p.R, p.h - r0), c = sb * 512 + 16 * lane;
+    const bool     in = c < p.w;
+    const uint8_t *src = p.img + (size_t)r0 * p.w + c;
+    unsigned       lo[4] = {0, 0, 0, 0}, hi[4] = {0, 0, 0, 0};
+    for (unsigned i0 = 0; i0 < rows; i0 += 8) {
+        uint4 x[8];
 #pragma unroll
-            for (unsigned k = 0; k < 8; k++)
-                t[k] = b0 + k < p.nbands ? m[(size_t)(b0 + k) * p.wp] : 0u;
+        for (unsigned k = 0; k < 8; k++)
+            x[k] = (in && i0 + k < rows) ? ld_stream_u4(src + (size_t)(i0 + k) * p.w) : make_uint4(0, 0, 0, 0);
 #pragma unroll
-            for (unsigned k = 0; k < 8; k++) {
-                if (b0 + k < p.nbands)
-                    m[(size_t)(b0 + k) * p.wp] = run;
-                run += t[k];
+        for (unsigned k = 0; k < 8; k++) {
+            const unsigned v[4] = {x[k].x, x[k].y, x[k].z, x[k].w};
+            unsigned       t = 0;
+#pragma unroll
+            for (unsigned q = 0; q < 4; q++) {
+                lo[q] += v[q] & 0x00ff00ffu;
+                hi[q] += (v[q] >> 8) & 0x00ff00ffu;
+                t = __dp4a(v[q], 0x01010101u, t);
             }
+            t += __shfl_xor_sync(0xffffffffu, t, 1);
+            t += __shfl_xor_sync(0xffffffffu, t, 2);
+            t += __shfl_xor_sync(0xffffffffu, t, 4);
+            // every lane of an 8-lane group now holds its block's sum of this row: lane k of the group stores it
+            // (one 4-byte store per 128 pixels)
+            if ((lane & 7) == k && i0 + k < rows && sb * 4 + (lane >> 3) < p.nblk)
+                p.rowcarry[(size_t)(r0 + i0 + k) * p.nblk + sb * 4 + (lane >> 3)] = t;
         }
-    } else {
-        const unsigned r = (blockIdx.x - p.nblk) * 128 + threadIdx.x;
-        if (r >= p.h)
-            return;
-        uint32_t *m   = p.rowcarry + (size_t)r * p.nblk;
-        unsigned  run = 0;
-        for (unsigned j0 = 0; j0 < p.nblk; j0 += 8) {
-            unsigned t[8];
+    }
+    if (c < p.wp) {
+        uint4 *dst = reinterpret_cast<uint4 *>(p.colcarry + (size_t)b * p.wp + c);
 #pragma unroll
-            for (unsigned k = 0; k < 8; k++)
-                t[k] = j0 + k < p.nblk ? m[j0 + k] : 0u;
+        for (unsigned q = 0; q < 4; q++)
+            dst[q] = make_uint4(lo[q] & 0xffffu, hi[q] & 0xffffu, lo[q] >> 16, hi[q] >> 16);
+    }
+}
+
+// Column carries: exclusive prefix down the bands.  One CTA per 32 columns, warp k takes a contiguous run of bands
+// (128-byte row segments), the runs are chained through shared memory; the second read of a run hits L1/L2.
+__device__ __forceinline__ void ii_rowprefix(const IIParams &p, unsigned r, unsigned lane);
+
+__global__ void __launch_bounds__(1024) ii_prefix_kernel(const IIParams p, const unsigned col_ctas)
+{
+    __shared__ unsigned s_tot[32][33];
+    const unsigned lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (blockIdx.x >= col_ctas) { // the other role of this launch: 32 image rows per CTA, one warp each
+        ii_rowprefix(p, (blockIdx.x - col_ctas) * 32 + wid, lane);
+        return;
+    }
+    const unsigned per = (p.nbands + 31) / 32, b0 = wid * per, b1 = min(p.nbands, b0 + per);
+    uint32_t      *m = p.colcarry + (size_t)blockIdx.x * 32 + lane;
+    unsigned       sum = 0;
+    for (unsigned b = b0; b < b1; b += 8) {
+        unsigned t[8];
 #pragma unroll
-            for (unsigned k = 0; k < 8; k++) {
-                if (j0 + k < p.nblk)
-                    m[j0 + k] = run;
-                run += t[k];
-            }
+        for (unsigned k = 0; k < 8; k++)
+            t[k] = b + k < b1 ? m[(size_t)(b + k) * p.wp] : 0u;
+#pragma unroll
+        for (unsigned k = 0; k < 8; k++)
+            sum += t[k];
+    }
+    s_tot[wid][lane] = sum;
+    __syncthreads();
+    unsigned run = 0;
+    for (unsigned k = 0; k < wid; k++)
+        run += s_tot[k][lane];
+    for (unsigned b = b0; b < b1; b += 8) {
+        unsigned t[8];
+#pragma unroll
+        for (unsigned k = 0; k < 8; k++)
+            t[k] = b + k < b1 ? m[(size_t)(b + k) * p.wp] : 0u;
+#pragma unroll
+        for (unsigned k = 0; k < 8; k++) {
+            if (b + k < b1)
+                m[(size_t)(b + k) * p.wp] = run;
+            run += t[k];
         }
+    }
+}
+
+// Row carries: exclusive prefix along the blocks of every image row, one warp per row.
+__device__ __forceinline__ void ii_rowprefix(const IIParams &p, unsigned r, unsigned lane)
+{
+    if (r >= p.h)
+        return;
+    uint32_t *m   = p.rowcarry + (size_t)r * p.nblk;
+    unsigned  run = 0;
+    for (unsigned j0 = 0; j0 < p.nblk; j0 += 32) {
+        const unsigned t   = j0 + lane < p.nblk ? m[j0 + lane] : 0u;
+        unsigned       inc = t;
+#pragma unroll
+        for (unsigned d = 1; d < 32; d <<= 1) {
+            const unsigned n = __shfl_up_sync(0xffffffffu, inc, d);
+            if (lane >= d)
+                inc += n;
+        }
+        if (j0 + lane < p.nblk)
+            m[j0 + lane] = run + inc - t;
+        run += __shfl_sync(0xffffffffu, inc, 31);
     }
 }
 
@@ -127,29 +202,14 @@ __global__ void __launch_bounds__(kIIWarps * 32) ii_write_kernel(const IIParams 
     const unsigned left = lane < rows ? p.rowcarry[(size_t)(r0 + lane) * p.nblk + j] : 0u;
     uint4          acc  = *reinterpret_cast<const uint4 *>(p.colcarry + (size_t)b * p.wp + c);
 
-    // two rows per iteration: their lane totals (<= 1020 each, <= 32640 per warp) share one 32-bit warp scan
-    for (unsigned i = 0; i < rows; i += 2) {
-        const bool     two = i + 1 < rows;
-        const unsigned xa = load_px4<kAligned>(p, r0 + i, c);
-        const unsigned xb = two ? load_px4<kAligned>(p, r0 + i + 1, c) : 0u;
-        const unsigned a0 = xa & 0xff, a1 = a0 + ((xa >> 8) & 0xff), a2 = a1 + ((xa >> 16) & 0xff), a3 = a2 + (xa >> 24);
-        const unsigned b0 = xb & 0xff, b1 = b0 + ((xb >> 8) & 0xff), b2 = b1 + ((xb >> 16) & 0xff), b3 = b2 + (xb >> 24);
-        const unsigned tot = a3 | (b3 << 16);
-        unsigned       inc = tot;
-#pragma unroll
-        for (unsigned d = 1; d < 32; d <<= 1) {
-            const unsigned n = __shfl_up_sync(0xffffffffu, inc, d);
-            if (lane >= d)
-                inc += n;
-        }
-        const unsigned exc   = inc - tot;
-        const unsigned baseA = (exc & 0xffffu) + __shfl_sync(0xffffffffu, left, i);
-        const unsigned baseB = (exc >> 16) + __shfl_sync(0xffffffffu, left, (i + 1) & 31);
-        acc.x += baseA + a0;
-        acc.y += baseA + a1;
-        acc.z += baseA + a2;
-        acc.w += baseA + a3;
-        uint32_t *o = p.out + (size_t)(r0 + i) * p.w + c;
+    auto emit = [&](unsigned row, unsigned base, unsigned q0, unsigned q1, unsigned q2, unsigned q3) {
+        acc.x += base + q0;
+        acc.y += base + q1;
+        acc.z += base + q2;
+        acc.w += base + q3;
+        if (row >= rows)
+            return;
+        uint32_t *o = p.out + (size_t)(r0 + row) * p.w + c;
         if (kAligned) {
             if (c < p.w)
                 st_stream_u4(o, acc);
@@ -159,21 +219,30 @@ __global__ void __launch_bounds__(kIIWarps * 32) ii_write_kernel(const IIParams 
             if (c + 2 < p.w) o[2] = acc.z;
             if (c + 3 < p.w) o[3] = acc.w;
         }
-        if (two) {
-            acc.x += baseB + b0;
-            acc.y += baseB + b1;
-            acc.z += baseB + b2;
-            acc.w += baseB + b3;
-            o += p.w;
-            if (kAligned) {
-                if (c < p.w)
-                    st_stream_u4(o, acc);
-            } else {
-                if (c < p.w) o[0] = acc.x;
-                if (c + 1 < p.w) o[1] = acc.y;
-                if (c + 2 < p.w) o[2] = acc.z;
-                if (c + 3 < p.w) o[3] = acc.w;
+    };
+    // kIIBatch rows per iteration (all loads first); two rows share one 32-bit warp scan: their lane totals
+    // (<= 1020 each, <= 32640 per warp) sit in the two 16-bit halves
+    for (unsigned i0 = 0; i0 < rows; i0 += kIIBatch) {
+        unsigned x[kIIBatch];
+#pragma unroll
+        for (unsigned k = 0; k < kIIBatch; k++)
+            x[k] = i0 + k < rows ? load_px4<kAligned>(p, r0 + i0 + k, c) : 0u;
+#pragma unroll
+        for (unsigned k = 0; k < kIIBatch; k += 2) {
+            const unsigned i = i0 + k, xa = x[k], xb = x[k + 1];
+            const unsigned a0 = xa & 0xff, a1 = a0 + ((xa >> 8) & 0xff), a2 = a1 + ((xa >> 16) & 0xff), a3 = a2 + (xa >> 24);
+            const unsigned b0 = xb & 0xff, b1 = b0 + ((xb >> 8) & 0xff), b2 = b1 + ((xb >> 16) & 0xff), b3 = b2 + (xb >> 24);
+            const unsigned tot = a3 | (b3 << 16);
+            unsigned       inc = tot;
+#pragma unroll
+            for (unsigned d = 1; d < 32; d <<= 1) {
+                const unsigned n = __shfl_up_sync(0xffffffffu, inc, d);
+                if (lane >= d)
+                    inc += n;
             }
+            const unsigned exc = inc - tot;
+            emit(i, (exc & 0xffffu) + __shfl_sync(0xffffffffu, left, i & 31), a0, a1, a2, a3);
+            emit(i + 1, (exc >> 16) + __shfl_sync(0xffffffffu, left, (i + 1) & 31), b0, b1, b2, b3);
         }
     }
 }
@@ -227,12 +296,16 @@ extern "C" int b200_integral_image_u8_async(uint32_t *d_out, const uint8_t *d_im
     p.rowcarry = reinterpret_cast<uint32_t *>(reinterpret_cast<char *>(c->image.ptr) + ((col_bytes + 255) & ~(size_t)255));
     const bool aligned = (p.w % 4 == 0) && (((uintptr_t)d_img) % 4 == 0) && (((uintptr_t)d_out) % 16 == 0);
     const unsigned grid = (p.ntiles + kIIWarps - 1) / kIIWarps;
-    if (aligned)
+    const bool aligned16 = (p.w % 16 == 0) && (((uintptr_t)d_img) % 16 == 0);
+    if (aligned16) {
+        const unsigned t16 = p.nbands * ((p.nblk + 3) / 4);
+        ii_sums16_kernel<<<(t16 + kIIWarps - 1) / kIIWarps, kIIWarps * 32, 0, stream>>>(p);
+    } else if (aligned)
         ii_sums_kernel<true><<<grid, kIIWarps * 32, 0, stream>>>(p);
     else
         ii_sums_kernel<false><<<grid, kIIWarps * 32, 0, stream>>>(p);
     B200_TRY(cudaGetLastError());
-    ii_prefix_kernel<<<p.nblk + (p.h + 127) / 128, 128, 0, stream>>>(p);
+    ii_prefix_kernel<<<p.wp / 32 + (p.h + 31) / 32, 1024, 0, stream>>>(p, p.wp / 32);
     B200_TRY(cudaGetLastError());
     count_launch(2);
     {
