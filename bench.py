@@ -216,6 +216,19 @@ def primitives_table(torch, dist, prim, mg, rank, world, peak, barrier, p2p=Fals
         it[0] += 1
     record("histogram256_64MiB", time_steps(torch, step256, 40, 8) / 40, n64, {"l2": "4 rotating inputs (256 MiB)"}, 1)
     record("histogram64_64MiB", time_steps(torch, step64, 40, 8) / 40, n64, {"l2": "4 rotating inputs (256 MiB)"}, 1)
+    # the same 40 calls replayed from a CUDA graph (a 10 us kernel is comparable to the launch latency
+    # of a Python/ctypes loop, ~11 us per call on this host)
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=side):
+            for _ in range(40):
+                step256()
+        record("histogram256_64MiB_cuda_graph", time_steps(torch, g.replay, 5, 2) / (5 * 40), n64,
+               {"l2": "4 rotating inputs (256 MiB)", "note": "40 calls per graph replay"}, 1)
+        del g
+    torch.cuda.current_stream().wait_stream(side)
     del bufs
     # --- histogram, 4 GiB per GPU, both histograms in one pass (BASELINE configs[3] shape: 32 GiB over 8)
     big = 4 << 30
@@ -263,6 +276,17 @@ def primitives_table(torch, dist, prim, mg, rank, world, peak, barrier, p2p=Fals
         kept = int(cnt.item())
         record("filter_arr_compaction_2^28", t_c, 4 * N_ELEMS + 4 * kept,
                {"kept": kept, "note": "4 B read per element + 4 B written per kept element, output in input order"})
+        # integral image (shfl_scan's second test) at an HBM-sized image and at the sample's 1920 x 1080
+        for ih, iw, reps in ((16384, 16384, 10), (1080, 1920, 50)):
+            img = torch.empty(ih * iw, dtype=torch.uint8, device="cuda")
+            prim.generate(img, "bytes", 0, ih * iw, 11)
+            ii_out = dst[:ih * iw]
+
+            def step_ii():
+                prim.integral_image(ii_out, img, iw, ih)
+            record("integral_image_%dx%d" % (iw, ih), time_steps(torch, step_ii, reps, 4) / reps, 5 * ih * iw,
+                   {"note": "1 B read + 4 B written per pixel; the band sums re-read the image (6 B/pixel moved)"})
+            del img
     del src, dst
     # --- reduction sibling: batched dot products, 4096 vectors x 65536 floats (2 GiB read)
     if world == 1:

@@ -28,15 +28,24 @@ namespace cg = cooperative_groups;
 namespace b200 {
 
 constexpr int kHistThreads = 1024;
-constexpr int kHistUnroll  = 8;
+#ifndef B200_HIST_UNROLL
+#define B200_HIST_UNROLL 8
+#endif
+#ifndef B200_HIST_EARLY
+#define B200_HIST_EARLY 0
+#endif
+constexpr int kHistUnroll  = B200_HIST_UNROLL;
 
 // kHistFusedP2P: the fused mode whose last CTA also all-reduces the 256 bins over the NVLink peer windows (p2p.cuh)
 enum HistMode { kHist256 = 0, kHist64 = 1, kHistFused = 2, kHistFusedP2P = 3 };
 
-// scratch layout (u32 words): [0] ticket, [4..260) acc256, [260..324) acc64
+// scratch layout (u32 words): [0] ticket, [4..260) acc256 (the peer-exchange mode's u32 accumulator), [260..324)
+// unused, from word 328: 256 + 64 u64 accumulators {contributions so far << 40 | sum} of the single-GPU modes
 constexpr int kHistAcc256 = 4;
 constexpr int kHistAcc64  = 260;
-constexpr int kHistWords  = 324;
+constexpr int kHistAccU64 = 328;
+constexpr int kHistWords  = kHistAccU64 + 2 * (256 + 64);
+constexpr unsigned long long kHistOne = 1ull << 40; // a cluster's bin count is < 2^32 and there are < 2^8 clusters
 
 template <int BINS, int SH> __device__ __forceinline__ void count_word(unsigned *table, unsigned lane4, unsigned w)
 {
@@ -76,13 +85,6 @@ __global__ void __launch_bounds__(kHistThreads, 1)
     const unsigned    lane    = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const unsigned    lane4   = lane * 4;
 
-    for (int i = threadIdx.x; i < BINS * 32; i += kHistThreads)
-        table[i] = 0;
-    if (threadIdx.x < BINS)
-        merged[threadIdx.x] = 0;
-    __syncthreads();
-
-    // ---- count ----------------------------------------------------------------------------------
     const uintptr_t addr = (uintptr_t)data;
     size_t          head = (16 - (addr & 15)) & 15;
     if (head > n)
@@ -92,6 +94,31 @@ __global__ void __launch_bounds__(kHistThreads, 1)
     const uint4 *vin    = reinterpret_cast<const uint4 *>(data + head);
     const size_t stride = (size_t)gridDim.x * kHistThreads;
     size_t       v      = (size_t)blockIdx.x * kHistThreads + threadIdx.x;
+#if B200_HIST_EARLY
+    // the first round of loads is in flight while the table is zeroed (short inputs: the fill latency counts)
+    uint4      r0[kHistUnroll];
+    const bool early = v + (kHistUnroll - 1) * stride < nvec;
+    if (early) {
+#pragma unroll
+        for (int k = 0; k < kHistUnroll; k++)
+            r0[k] = ld_stream_u4(vin + v + k * stride);
+    }
+#endif
+    for (int i = threadIdx.x; i < BINS * 32; i += kHistThreads)
+        table[i] = 0;
+    if (threadIdx.x < BINS)
+        merged[threadIdx.x] = 0;
+    __syncthreads();
+
+    // ---- count ----------------------------------------------------------------------------------
+#if B200_HIST_EARLY
+    if (early) {
+#pragma unroll
+        for (int k = 0; k < kHistUnroll; k++)
+            count_vec<BINS, SH>(table, lane4, r0[k]);
+        v += kHistUnroll * stride;
+    }
+#endif
     for (; v + (kHistUnroll - 1) * stride < nvec; v += kHistUnroll * stride) {
         uint4 r[kHistUnroll];
 #pragma unroll
@@ -142,7 +169,37 @@ __global__ void __launch_bounds__(kHistThreads, 1)
     if (crank != 0)
         return;
 
-    // ---- leader: one global reduction per bin, last leader publishes --------------------------------
+    // ---- leader, single-GPU modes: ONE 64-bit atomic per bin carries the count and the number of clusters that
+    // have contributed; the thread that completes a bin writes it out and re-arms the accumulator.  No fence, no
+    // ticket, no second pass over the accumulator: the finish is a single L2 round trip.
+    if (MODE != kHistFusedP2P) {
+        unsigned long long *acc64 = reinterpret_cast<unsigned long long *>(scratch + kHistAccU64);
+        const unsigned      nclus = gridDim.x / csize;
+        if (threadIdx.x < BINS) {
+            const unsigned      mine = merged[threadIdx.x];
+            unsigned long long *a    = acc64 + ((MODE == kHist64) ? 256 : 0) + threadIdx.x;
+            const unsigned long long old = atomicAdd(a, kHistOne | mine);
+            if ((unsigned)(old >> 40) == nclus - 1) {
+                *a = 0;
+                (MODE == kHist64 ? out64 : out256)[threadIdx.x] = (unsigned)old + mine;
+            }
+            if (MODE == kHistFused) { // 4 adjacent 256-bins make one 64-bin (exact: histogram_gold.cpp:41-44)
+                unsigned s4 = mine + __shfl_xor_sync(0xffffffffu, mine, 1);
+                s4 += __shfl_xor_sync(0xffffffffu, s4, 2);
+                if ((threadIdx.x & 3) == 0) {
+                    unsigned long long      *b    = acc64 + 256 + (threadIdx.x >> 2);
+                    const unsigned long long old4 = atomicAdd(b, kHistOne | s4);
+                    if ((unsigned)(old4 >> 40) == nclus - 1) {
+                        *b                       = 0;
+                        out64[threadIdx.x >> 2] = (unsigned)old4 + s4;
+                    }
+                }
+            }
+        }
+        return;
+    }
+
+    // ---- leader, peer-exchange mode: one global reduction per bin, the last leader (ticket) runs the exchange ------
     unsigned *ticket = scratch;
     unsigned *acc    = scratch + ((MODE == kHist64) ? kHistAcc64 : kHistAcc256);
     if (threadIdx.x < BINS)
@@ -194,7 +251,7 @@ __global__ void __launch_bounds__(kHistThreads, 1)
         *ticket = 0;
 }
 
-static int g_hist_cluster = 2; // CTAs per cluster (1, 2, 4 or 8); 2 packs 148 SMs exactly
+static int g_hist_cluster = 0; // CTAs per cluster (1, 2, 4 or 8; 2 packs 148 SMs exactly); 0 = by input size
 
 template <int MODE>
 static int launch_hist(unsigned *out256, unsigned *out64, const void *d_data, size_t n, cudaStream_t stream,
@@ -205,7 +262,9 @@ static int launch_hist(unsigned *out256, unsigned *out64, const void *d_data, si
     if (!c)
         return st;
     B200_TRY((cudaError_t)ensure(c->hist, kHistWords * sizeof(unsigned), stream));
-    const int cluster = g_hist_cluster;
+    // short inputs skip the two cluster barriers of the DSMEM merge (64 MiB: 16.9 vs 18.2 us); from 128 MiB on the
+    // merge is free and halves the global atomics
+    const int cluster = g_hist_cluster ? g_hist_cluster : (n < (128u << 20) ? 1 : 2);
     // persistent: one CTA per SM, but never more CTAs than there are 16 KiB slabs of input
     size_t want = (n / 16 + kHistThreads - 1) / kHistThreads;
     int    grid = (int)(want < (size_t)c->num_sms ? want : (size_t)c->num_sms);
@@ -233,7 +292,7 @@ static int launch_hist(unsigned *out256, unsigned *out64, const void *d_data, si
 
 int set_hist_cluster(int cluster)
 {
-    if (cluster != 1 && cluster != 2 && cluster != 4 && cluster != 8)
+    if (cluster != 0 && cluster != 1 && cluster != 2 && cluster != 4 && cluster != 8)
         return (int)cudaErrorInvalidValue;
     g_hist_cluster = cluster;
     return 0;

@@ -71,7 +71,7 @@ if "hist" in what:
         lib.b200_tune_hist_cluster(cl)
         us = timeit(step, 40, 8)
         print("hist256 64 MiB cluster=%d: %7.2f us  %7.1f GB/s" % (cl, us, n / us / 1e3))
-    lib.b200_tune_hist_cluster(2)
+    lib.b200_tune_hist_cluster(0)
     del bufs
     big = torch.empty(4 << 30, dtype=torch.uint8, device="cuda")
     prim.generate(big, "bytes", 0, 4 << 30, 2009)

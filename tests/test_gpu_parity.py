@@ -121,7 +121,7 @@ def test_histogram_cluster_sizes(prim, cluster):
         assert (run_hist(prim, d, h.size, "256") == oracle.histogram256(h)).all()
         assert (run_hist(prim, d, 5000, "64") == oracle.histogram64(h[:5000])).all()
     finally:
-        check(lib.b200_tune_hist_cluster(2), "tune")
+        check(lib.b200_tune_hist_cluster(0), "tune")
 
 
 def test_histogram_dropin_symbols(prim):
@@ -619,8 +619,12 @@ def test_entry_points_capture_into_a_cuda_graph_and_replay(prim):
     red = torch.empty(4, dtype=torch.int32, device="cuda")
     scan_out = torch.empty(n, dtype=torch.int32, device="cuda")
     dk, dv, bk, bv = (torch.empty(n, dtype=torch.int32, device="cuda") for _ in range(4))
+    ii = torch.empty(n, dtype=torch.int32, device="cuda")
+    comp, ncomp = torch.empty(n, dtype=torch.int32, device="cuda"), torch.empty(1, dtype=torch.int32, device="cuda")
 
     def enqueue():
+        prim.integral_image(ii, data, 2048, n // 2048)   # 4 launches incl. the library's own batched scan
+        prim.filter_arr(comp, ncomp, xi, n)
         prim.histogram256(h256, data, n)
         prim.histogram64(h64, data, n)
         prim.reduce(n, 256, 4, 7, xi, red)
@@ -630,7 +634,7 @@ def test_entry_points_capture_into_a_cuda_graph_and_replay(prim):
     def fill(seed):
         r = np.random.default_rng(seed)
         hb = r.integers(0, 256, n, dtype=np.uint8)
-        hx_ = r.integers(0, 2**31, n, dtype=np.int64).astype(np.int32)
+        hx_ = (r.integers(0, 2**31, n, dtype=np.int64) - (1 << 29)).astype(np.int32)
         hk = r.integers(0, 2**32, n, dtype=np.uint32)
         data.copy_(torch.from_numpy(hb))
         xi.copy_(torch.from_numpy(hx_))
@@ -646,6 +650,9 @@ def test_entry_points_capture_into_a_cuda_graph_and_replay(prim):
         assert (scan_out.cpu().numpy().view(np.uint32) == oracle.scan_exclusive(hx_.view(np.uint32), 1, n)).all()
         wk, wv = oracle.stable_sort_kv(hk, np.arange(n, dtype=np.uint32), 1)
         assert (dk.cpu().numpy().view(np.uint32) == wk).all() and (dv.cpu().numpy().view(np.uint32) == wv).all()
+        assert (ii.cpu().numpy().view(np.uint32).reshape(-1, 2048) == oracle.integral_image(hb.reshape(-1, 2048))).all()
+        want = oracle.filter_positive(hx_)
+        assert int(ncomp.item()) == want.size and (comp[:want.size].cpu().numpy() == want).all()
 
     side = torch.cuda.Stream()
     with torch.cuda.stream(side):
