@@ -182,6 +182,48 @@ def run_reference(args):
     emit(line)
 
 
+def cpu_gold_table(oracle):
+    """The samples' CPU gold functions, single thread as shipped, each on a bounded sample of its bench workload.
+    `kind` = "reference" when the function ran from oracle/_ref (the reference's own sources compiled unmodified),
+    "port" for the restatement in oracle/oracle.c."""
+    import numpy as np
+    gold = oracle.ref if oracle.ref is not None else oracle
+    kind = "reference" if oracle.ref is not None else "port"
+    out = {}
+
+    def timed(fn, reps=3):
+        best = None
+        for _ in range(reps):
+            t0 = time.perf_counter()
+            fn()
+            dt = time.perf_counter() - t0
+            best = dt if best is None else min(best, dt)
+        return best
+
+    data = oracle.generate("bytes", 0, 64 << 20, 2009)
+    for name, fn in (("histogram256CPU", gold.histogram256), ("histogram64CPU", gold.histogram64)):
+        dt = timed(lambda: fn(data))
+        out[name] = {"GB/s": round(data.size / dt / 1e9, 3), "seconds": round(dt, 4), "sample": "64 MiB (the whole "
+                     "configs[0] input)", "cores": 1, "kind": kind}
+    n = 1 << 26
+    src = oracle.generate("u31", 0, n, 2009)
+    dt = timed(lambda: gold.scan_exclusive(src, 1, n))
+    out["scanExclusiveHost"] = {"GB/s": round(8 * n / dt / 1e9, 3), "seconds": round(dt, 4), "cores": 1, "kind": kind,
+                                "sample": "one array of 2^26 u32 (a quarter of the 2^28 bench array), 8 B per element"}
+    n = 1 << 20
+    keys = oracle.generate("key_unique", 0, n, 2009)
+    vals = np.arange(n, dtype=np.uint32)
+    dt = timed(lambda: gold.merge_sort_host(keys, vals, 1), 1)
+    out["mergeSortHost"] = {"Gkeys/s": round(n / dt / 1e9, 5), "seconds": round(dt, 3), "cores": 1, "kind": kind,
+                            "sample": "2^20 pairs, D1 unique keys (1/256 of the bench's 2^28; its merge levels grow "
+                                      "with log2 N, so 2^28 is slower per key)"}
+    img = oracle.generate("bytes", 0, 4096 * 4096, 11).reshape(4096, 4096)
+    dt = timed(lambda: oracle.integral_image(img))
+    out["integral_image"] = {"GB/s": round(5 * img.size / dt / 1e9, 3), "seconds": round(dt, 4), "cores": 1,
+                             "kind": "port", "sample": "4096 x 4096 u8 image, 5 B per pixel"}
+    return out
+
+
 # ---------------------------------------------------------------------------------- primitives table
 def primitives_table(torch, dist, prim, mg, rank, world, peak, barrier, p2p=False):
     """GB/s (Gkeys/s for sort) of every primitive of the path, device-resident inputs, CUDA events."""
@@ -444,6 +486,11 @@ def run_ours(args):
                   "float_rel_err": abs(gpu_f - cpu_f) / abs(cpu_f), "float_rel_err_e2e": abs(e_f - cpu_f) / abs(cpu_f),
                   "float_tolerance": 1e-5}
 
+    # ---- the other primitives' gold functions on the same host cores, bounded samples, 1 thread each
+    cpu_gold = None
+    if world == 1 and not args.skip_table:
+        cpu_gold = cpu_gold_table(oracle)
+
     traffic = None
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
@@ -463,7 +510,7 @@ def run_ours(args):
                          "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
                          "frac_of_nominal_8TBs": achieved / HBM_NOMINAL, "traffic": traffic,
                          "algorithmic_bytes_per_launch": 4 * N_ELEMS},
-            "cpu_baseline": cpu, "clocks": clocks,
+            "cpu_baseline": cpu, "cpu_gold": cpu_gold, "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": 2 * 4 * N_ELEMS,
                     "d2h_bytes_per_step": 8, "steps": e2e_steps,
                     "api": "b200_reduce_i32_host + b200_reduce_f32_host (pinned host input, chunked H2D overlap)"},
