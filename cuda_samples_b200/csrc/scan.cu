@@ -643,15 +643,26 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
             const unsigned e0 = run + (inc[r] - tot[r]);
             run += __shfl_sync(0xffffffffu, inc[r], 31);
             if (kCompact) { // zeros stand in for elements beyond `count`: never kept
-                unsigned pos = e0;
+                // the row's kept elements are packed in the warp's 512-byte slab first, so that they leave as full
+                // 128-byte store instructions (lane-private stores straight from the registers touch 4x the sectors)
+                unsigned *slab = reinterpret_cast<unsigned *>(smem_raw + sizeof(Smem)) + (warp & (kScanWarps - 1)) * 128;
+                unsigned  pos  = inc[r] - tot[r];
                 if ((int)v[r].x > 0)
-                    dst[pos++] = v[r].x;
+                    slab[pos++] = v[r].x;
                 if ((int)v[r].y > 0)
-                    dst[pos++] = v[r].y;
+                    slab[pos++] = v[r].y;
                 if ((int)v[r].z > 0)
-                    dst[pos++] = v[r].z;
+                    slab[pos++] = v[r].z;
                 if ((int)v[r].w > 0)
-                    dst[pos++] = v[r].w;
+                    slab[pos++] = v[r].w;
+                const unsigned kept  = __shfl_sync(0xffffffffu, inc[r], 31);
+                const unsigned start = __shfl_sync(0xffffffffu, e0, 0);
+                __syncwarp();
+#pragma unroll
+                for (int q = 0; q < 4; q++)
+                    if (q * 32 + lane < kept)
+                        dst[start + q * 32 + lane] = slab[q * 32 + lane];
+                __syncwarp();
                 continue;
             }
             uint4 o;
@@ -829,10 +840,11 @@ int compact_tma(int32_t *d_dst, int32_t *d_count, const int32_t *d_src, size_t n
     static bool prepared = false;
     if (!prepared) {
         B200_TRY(cudaFuncSetAttribute(scan_tma_kernel<5, 5, 3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)sizeof(ScanTmaSmem<5, 5>)));
+                                      (int)(sizeof(ScanTmaSmem<5, 5>) + kScanWarps * 512)));
         prepared = true;
     }
-    scan_tma_kernel<5, 5, 3, true><<<grid, kTmaThreads, sizeof(ScanTmaSmem<5, 5>), stream>>>(
+    // + one 512-byte packing slab per scan warp behind the pipeline's shared memory
+    scan_tma_kernel<5, 5, 3, true><<<grid, kTmaThreads, sizeof(ScanTmaSmem<5, 5>) + kScanWarps * 512, stream>>>(
         reinterpret_cast<unsigned *>(d_dst), reinterpret_cast<const unsigned *>(d_src), p, st64, desc);
     count_launch();
     B200_TRY(cudaGetLastError());

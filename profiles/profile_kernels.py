@@ -53,6 +53,16 @@ if which in ("all", "scan"):
     torch.cuda.synchronize()
     del src, dst
 
+if which in ("all", "image"):
+    ih = iw = 16384
+    img = torch.empty(ih * iw, dtype=torch.uint8, device="cuda")
+    prim.generate(img, "bytes", 0, ih * iw, 11)
+    sat = torch.empty(ih * iw, dtype=torch.int32, device="cuda")
+    for _ in range(REPS):
+        prim.integral_image(sat, img, iw, ih)
+    torch.cuda.synchronize()
+    del img, sat
+
 if which in ("all", "sort"):
     sk = torch.empty(N, dtype=torch.int32, device="cuda")
     sv = torch.arange(N, dtype=torch.int32, device="cuda")
