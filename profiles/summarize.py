@@ -40,6 +40,13 @@ def main(rep, out):
         summary["reduce_kernel"] = max(red)
     summary["_source"] = os.path.basename(rep) + ": ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per launch"
     tj = os.path.join(os.path.dirname(os.path.abspath(out)), "traffic.json")
+    try:  # a capture restricted with -k keeps the other kernels' earlier figures
+        with open(tj) as f:
+            for k, v in json.load(f).items():
+                if k not in summary and not k.startswith("_"):
+                    summary[k] = v
+    except Exception:
+        pass
     with open(tj, "w") as f:
         json.dump(summary, f, indent=1, sort_keys=True)
     print("wrote", out, tj)
