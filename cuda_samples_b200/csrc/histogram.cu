@@ -27,7 +27,11 @@ namespace cg = cooperative_groups;
 
 namespace b200 {
 
-constexpr int kHistThreads = 1024;
+#ifndef B200_HIST_THREADS
+#define B200_HIST_THREADS 1024
+#endif
+constexpr int kHistThreads = B200_HIST_THREADS;          // 1024 x 1 CTA per SM (default) or 512 x 2
+constexpr int kHistCtasPerSm = 1024 / kHistThreads;
 #ifndef B200_HIST_UNROLL
 #define B200_HIST_UNROLL 8
 #endif
@@ -69,7 +73,7 @@ template <int BINS, int SH> __device__ __forceinline__ void count_vec(unsigned *
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(kHistThreads, 1)
+__global__ void __launch_bounds__(kHistThreads, kHistCtasPerSm)
     histogram_kernel(const unsigned char *__restrict__ data, size_t n, unsigned *__restrict__ out256,
                      unsigned *__restrict__ out64, unsigned *__restrict__ scratch, P2PArgs p2p)
 {
@@ -148,7 +152,7 @@ __global__ void __launch_bounds__(kHistThreads, 1)
     __syncthreads();
 
     // ---- fold the 32 lane columns: warp w owns rows [w*BINS/32, (w+1)*BINS/32) -------------------
-    constexpr int kRowsPerWarp = BINS / 32;
+    constexpr int kRowsPerWarp = BINS / (kHistThreads / 32);
     unsigned      mine         = 0; // lane r (< kRowsPerWarp) keeps the total of row warp*kRowsPerWarp + r
 #pragma unroll
     for (int r = 0; r < kRowsPerWarp; r++) {
@@ -267,7 +271,8 @@ static int launch_hist(unsigned *out256, unsigned *out64, const void *d_data, si
     const int cluster = g_hist_cluster ? g_hist_cluster : (n < (128u << 20) ? 1 : 2);
     // persistent: one CTA per SM, but never more CTAs than there are 16 KiB slabs of input
     size_t want = (n / 16 + kHistThreads - 1) / kHistThreads;
-    int    grid = (int)(want < (size_t)c->num_sms ? want : (size_t)c->num_sms);
+    const size_t slots = (size_t)c->num_sms * kHistCtasPerSm;
+    int    grid = (int)(want < slots ? want : slots);
     grid        = (grid / cluster) * cluster;
     if (grid < cluster)
         grid = cluster;

@@ -139,53 +139,63 @@ __global__ void __launch_bounds__(1024) ii_prefix_kernel(const IIParams p, const
     }
     const unsigned per = (p.nbands + 31) / 32, b0 = wid * per, b1 = min(p.nbands, b0 + per);
     uint32_t      *m = p.colcarry + (size_t)blockIdx.x * 32 + lane;
-    unsigned       sum = 0;
-    for (unsigned b = b0; b < b1; b += 8) {
-        unsigned t[8];
+    // the first 16 bands of the run stay in registers between the two phases (up to 512 bands = 16384 rows at
+    // R = 32 that is the whole run); longer runs re-read the rest, which the first phase left in L2
+    unsigned t[16], sum = 0;
 #pragma unroll
-        for (unsigned k = 0; k < 8; k++)
-            t[k] = b + k < b1 ? m[(size_t)(b + k) * p.wp] : 0u;
-#pragma unroll
-        for (unsigned k = 0; k < 8; k++)
-            sum += t[k];
+    for (unsigned k = 0; k < 16; k++) {
+        t[k] = b0 + k < b1 ? m[(size_t)(b0 + k) * p.wp] : 0u;
+        sum += t[k];
     }
+    for (unsigned b = b0 + 16; b < b1; b++)
+        sum += m[(size_t)b * p.wp];
     s_tot[wid][lane] = sum;
     __syncthreads();
     unsigned run = 0;
     for (unsigned k = 0; k < wid; k++)
         run += s_tot[k][lane];
-    for (unsigned b = b0; b < b1; b += 8) {
-        unsigned t[8];
 #pragma unroll
-        for (unsigned k = 0; k < 8; k++)
-            t[k] = b + k < b1 ? m[(size_t)(b + k) * p.wp] : 0u;
-#pragma unroll
-        for (unsigned k = 0; k < 8; k++) {
-            if (b + k < b1)
-                m[(size_t)(b + k) * p.wp] = run;
-            run += t[k];
-        }
+    for (unsigned k = 0; k < 16; k++) {
+        if (b0 + k < b1)
+            m[(size_t)(b0 + k) * p.wp] = run;
+        run += t[k];
+    }
+    for (unsigned b = b0 + 16; b < b1; b++) {
+        const unsigned x    = m[(size_t)b * p.wp];
+        m[(size_t)b * p.wp] = run;
+        run += x;
     }
 }
 
-// Row carries: exclusive prefix along the blocks of every image row, one warp per row.
+// Row carries: exclusive prefix along the blocks of every image row, one warp per row, four blocks per lane (one
+// round covers 128 blocks = 16384 columns).
 __device__ __forceinline__ void ii_rowprefix(const IIParams &p, unsigned r, unsigned lane)
 {
     if (r >= p.h)
         return;
     uint32_t *m   = p.rowcarry + (size_t)r * p.nblk;
     unsigned  run = 0;
-    for (unsigned j0 = 0; j0 < p.nblk; j0 += 32) {
-        const unsigned t   = j0 + lane < p.nblk ? m[j0 + lane] : 0u;
-        unsigned       inc = t;
+    for (unsigned j0 = 0; j0 < p.nblk; j0 += 128) {
+        const unsigned j = j0 + 4 * lane;
+        unsigned       t[4];
+#pragma unroll
+        for (unsigned k = 0; k < 4; k++)
+            t[k] = j + k < p.nblk ? m[j + k] : 0u;
+        const unsigned tot = (t[0] + t[1]) + (t[2] + t[3]);
+        unsigned       inc = tot;
 #pragma unroll
         for (unsigned d = 1; d < 32; d <<= 1) {
             const unsigned n = __shfl_up_sync(0xffffffffu, inc, d);
             if (lane >= d)
                 inc += n;
         }
-        if (j0 + lane < p.nblk)
-            m[j0 + lane] = run + inc - t;
+        unsigned e = run + inc - tot;
+#pragma unroll
+        for (unsigned k = 0; k < 4; k++) {
+            if (j + k < p.nblk)
+                m[j + k] = e;
+            e += t[k];
+        }
         run += __shfl_sync(0xffffffffu, inc, 31);
     }
 }
