@@ -850,3 +850,21 @@ def test_integral_image_band_heights_and_wrap(prim, rows, monkeypatch):
         assert (out.cpu().numpy().view(np.uint32).reshape(45, 77) == oracle.integral_image(img)).all()
     finally:
         knob.value = 0
+
+
+def test_size_limits_are_status_codes_not_aborts(prim):
+    """The extended ABI reports what it cannot do (documented limits in include/b200prim.h) as a status; nothing is
+    launched and the output stays untouched.  Empty inputs are a no-op."""
+    from cuda_samples_b200._lib import B200Error
+    out = torch.full((16,), 7, dtype=torch.int32, device="cuda")
+    img = torch.zeros(16, dtype=torch.uint8, device="cuda")
+    with pytest.raises(B200Error):
+        prim.integral_image(out, img, 1 << 16, 1 << 16)      # width * height = 2^32
+    with pytest.raises(B200Error):
+        prim.filter_arr(out, out, out, 1 << 30)              # n < 2^30
+    with pytest.raises(B200Error):
+        prim.mergeSort(out, out, out, out, out, out, 1 << 30, 1)
+    prim.integral_image(out, img, 0, 5)
+    prim.integral_image(out, img, 5, 0)
+    torch.cuda.synchronize()
+    assert bool((out == 7).all())
