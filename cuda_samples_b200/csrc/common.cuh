@@ -168,6 +168,20 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, unsigned parity)
                  "r"(parity)
                  : "memory");
 }
+// non-blocking: has the phase with this parity completed?
+__device__ __forceinline__ bool mbar_test(uint64_t *bar, unsigned parity)
+{
+    unsigned ok;
+    asm volatile("{\n"
+                 ".reg .pred p;\n"
+                 "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+                 "selp.u32 %0, 1, 0, p;\n"
+                 "}"
+                 : "=r"(ok)
+                 : "r"(smem_u32(bar)), "r"(parity)
+                 : "memory");
+    return ok != 0;
+}
 // global -> shared, completion signalled on an mbarrier (bytes: multiple of 16, both 16-B aligned)
 __device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gsrc, unsigned bytes, uint64_t *bar)
 {

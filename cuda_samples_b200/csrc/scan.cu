@@ -369,6 +369,9 @@ __device__ __forceinline__ bool window32(const unsigned long long *desc, long lo
 // one 2^28-element array (profiles/r01_scan_geometry_sweep.log): 24 KiB x 9 stages 520 us, 32 KiB x 6 434 us,
 // 40 KiB x 5 (phase A 3 ahead) 395 us, 48 KiB x 4 413 us, 64 KiB x 3 477 us.  Short arrays (a few tiles each)
 // prefer 32 KiB tiles that divide them evenly (16384 arrays of 16384: 344 us vs 396 us).
+#ifndef B200_SCAN_EAGER_B
+#define B200_SCAN_EAGER_B 0 // measured: 410 vs 396 us for one 2^28 array (phase A falls behind, look-backs get longer)
+#endif
 constexpr int      kTmaLookWarps = 2;
 constexpr int      kTmaThreads   = kScanThreads + 32 * (1 + kTmaLookWarps); // 16 scan + 1 producer + 2 look-back
 constexpr unsigned kTileEnd      = 0xffffffffu;
@@ -549,6 +552,21 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
         // ---- phase A: warp totals of tiles up to kTmaAhead ahead; the completing warp publishes -------
         while (end_index == 0xffffffffu && a <= b + kTmaAhead) {
             const unsigned s = a % kTmaStages;
+#if B200_SCAN_EAGER_B
+            if (a > b) {
+                // look-ahead is opportunistic: if the prefix of tile b arrives before tile a has landed, scan tile b
+                // first (its stage goes back to the producer sooner) and come back for tile a afterwards
+                bool landed, ready = false;
+                do {
+                    landed = __any_sync(0xffffffffu, mbar_test(&S.full[s], (a / kTmaStages) & 1));
+                    if (!landed)
+                        ready = __any_sync(0xffffffffu,
+                                           mbar_test(&S.prefix_ready[b % kTmaStages], (b / kTmaStages) & 1));
+                } while (!landed && !ready);
+                if (!landed)
+                    break;
+            }
+#endif
             mbar_wait(&S.full[s], (a / kTmaStages) & 1);
             const unsigned tile = S.tile[s];
             if (tile == kTileEnd) {

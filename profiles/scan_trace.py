@@ -16,17 +16,31 @@ from cuda_samples_b200._lib import lib  # noqa: E402
 
 N = 1 << 28
 lib.b200_tune_scan_backoff(int(os.environ.get('SCAN_BACKOFF', '0')))
-tiles = N // 8192
+tiles = -(-N // 10240)  # 40 KiB tiles (the geometry of arrays >= 2^20 elements)
 src = torch.empty(N, dtype=torch.int32, device="cuda")
 dst = torch.empty(N, dtype=torch.int32, device="cuda")
 prim.generate(src, "u31", 0, N, 2009)
+MODE = os.environ.get("SCAN_TRACE_MODE", "scan")  # "compact0": the compaction pipeline with nothing kept (no stores)
+cnt = torch.zeros(1, dtype=torch.int32, device="cuda")
+if MODE == "compact0":
+    src.neg_()
+    pass
+
+
+def run():
+    if MODE == "compact0":
+        prim.filter_arr(dst, cnt, src, N)
+    else:
+        prim.scanExclusiveLarge(dst, src, 1, N)
+
+
 for _ in range(3):
-    prim.scanExclusiveLarge(dst, src, 1, N)
+    run()
 trace = torch.zeros(tiles * 8, dtype=torch.int64, device="cuda")
 lib.b200_debug_set_scan_trace.argtypes = [ctypes.c_void_p]
 lib.b200_debug_set_scan_trace(ctypes.c_void_p(trace.data_ptr()))
 torch.cuda.synchronize()
-prim.scanExclusiveLarge(dst, src, 1, N)
+run()
 torch.cuda.synchronize()
 lib.b200_debug_set_scan_trace(ctypes.c_void_p(0))
 t = trace.cpu().numpy().reshape(tiles, 8).astype(np.float64)
