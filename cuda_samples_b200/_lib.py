@@ -65,6 +65,9 @@ SIGNATURES = {
                                               vp]),
     "b200_host_alloc": (ci, [ctypes.POINTER(vp), sz]),
     "b200_host_free": (ci, [vp]),
+    "b200_host_alloc_info": (ci, [vp] + [ctypes.POINTER(ci)] * 4),
+    "b200_host_probe_h2d": (ci, [vp, sz, ci, ctypes.POINTER(ctypes.c_double)]),
+    "b200_tune_host_path": (ci, [ci, sz]),
     "b200_tune_hist_cluster": (ci, [ci]),
     "b200_tune_scan_tma": (ci, [ci]),
     "b200_tune_scan_backoff": (ci, [ci]),

@@ -355,3 +355,51 @@ def sort_kv_host(h_dstKey, h_dstVal, h_srcKey, h_srcVal, N, sortDir):
     check(lib.b200_sort_kv_host(_hptr(h_dstKey), _hptr(h_dstVal), _hptr(h_srcKey), _hptr(h_srcVal), N, sortDir),
           "sort_kv_host")
     return h_dstKey, h_dstVal
+
+
+# ------------------------------------------------------------------ pinned, NUMA-local host buffers
+class HostBuffer:
+    """Pinned host memory from b200_host_alloc (registered + device-mapped, on the current GPU's NUMA node when the
+    platform allows).  `.array(dtype)` is a numpy view; free() (or the destructor) releases it."""
+
+    def __init__(self, nbytes):
+        p = ctypes.c_void_p(0)
+        check(lib.b200_host_alloc(ctypes.byref(p), nbytes), "b200_host_alloc")
+        self.ptr, self.nbytes = int(p.value), int(nbytes)
+
+    def array(self, dtype=np.uint8):
+        dt = np.dtype(dtype)
+        raw = (ctypes.c_char * self.nbytes).from_address(self.ptr)
+        a = np.frombuffer(raw, dtype=dt, count=self.nbytes // dt.itemsize)
+        a.flags.writeable = True
+        return a
+
+    def info(self):
+        v = [ctypes.c_int(-1) for _ in range(4)]
+        check(lib.b200_host_alloc_info(ctypes.c_void_p(self.ptr), *[ctypes.byref(x) for x in v]), "b200_host_alloc_info")
+        return {"gpu_numa_node": v[0].value, "mem_numa_node_first_page": v[1].value,
+                "mem_numa_node_last_page": v[2].value,
+                "placement": {0: "none possible", 1: "mbind", 2: "first touch on the node's CPUs"}.get(v[3].value)}
+
+    def free(self):
+        if self.ptr:
+            check(lib.b200_host_free(ctypes.c_void_p(self.ptr)), "b200_host_free")
+            self.ptr = 0
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+def host_probe_h2d(h_src, nbytes, reps=5):
+    """Plain pinned cudaMemcpyAsync host->device of nbytes, best of reps -> GB/s (the PCIe roofline of *_host)."""
+    g = ctypes.c_double(0.0)
+    check(lib.b200_host_probe_h2d(_hptr(h_src), nbytes, reps, ctypes.byref(g)), "b200_host_probe_h2d")
+    return float(g.value)
+
+
+def tune_host_path(mode, chunk_bytes=0):
+    """Experiments only: mode 0 = staged through device chunks, 1 = zero-copy for pinned input (default)."""
+    check(lib.b200_tune_host_path(mode, chunk_bytes), "b200_tune_host_path")

@@ -52,10 +52,31 @@ struct DeviceCtx {
     Scratch sort;         // digit histograms + descriptors
     Scratch image;        // integral image: band / block carries
     Scratch stage[2];     // device staging chunks of the host-buffer entry points
+    Scratch host_work;    // their own reduce scratch + chunk rows (never shared with the *_async entry points)
+    void   *host_slot = nullptr; // 4 KiB of mapped pinned host memory: results land here without a D2H copy
     cudaStream_t copy_stream[2] = {nullptr, nullptr}; // H2D / D2H engines of the host-buffer entry points
     cudaStream_t compute_stream = nullptr;
     cudaEvent_t  ev[6]          = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    unsigned     func_attr_mask = 0; // which kernels already have their >48 KiB dynamic-smem opt-in on THIS device
 };
+
+// cudaFuncSetAttribute is per device: every kernel that opts in to more than 48 KiB of dynamic shared memory does it
+// once per DeviceCtx (bit = one of the kAttr* ids), not once per process.
+enum FuncAttrBit : unsigned {
+    kAttrScanTma0 = 1u << 0, kAttrScanTma1 = 1u << 1, kAttrScanTma2 = 1u << 2, kAttrScanTma3 = 1u << 3,
+    kAttrSortHist4 = 1u << 4, kAttrSortPass0 = 1u << 5, kAttrSortPass1 = 1u << 6, kAttrSortPass2 = 1u << 7,
+    kAttrSortPass3 = 1u << 8, kAttrSortPass4 = 1u << 9, kAttrSortPass5 = 1u << 10, kAttrSortPeer = 1u << 11,
+    kAttrSegSort = 1u << 12, kAttrHist = 1u << 13, kAttrSortPassPk = 1u << 14, kAttrMisc0 = 1u << 15,
+    kAttrMisc1 = 1u << 16, kAttrMisc2 = 1u << 17, kAttrMisc3 = 1u << 18,
+};
+template <typename K> inline int opt_in_smem(DeviceCtx *c, unsigned bit, K kernel, size_t bytes)
+{
+    if (c->func_attr_mask & bit)
+        return 0;
+    B200_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    c->func_attr_mask |= bit;
+    return 0;
+}
 
 // Returns the context of the current device (created on first use).  nullptr + *status on error.
 DeviceCtx *ctx(int *status);

@@ -127,15 +127,3 @@ extern "C" int b200_release_scratch(void)
     release(c->stage[1]);
     return 0;
 }
-
-extern "C" int b200_host_alloc(void **h_ptr, size_t bytes)
-{
-    B200_TRY(cudaHostAlloc(h_ptr, bytes ? bytes : 1, cudaHostAllocDefault));
-    return 0;
-}
-
-extern "C" int b200_host_free(void *h_ptr)
-{
-    B200_TRY(cudaFreeHost(h_ptr));
-    return 0;
-}

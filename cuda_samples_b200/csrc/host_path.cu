@@ -10,7 +10,17 @@
 
 namespace b200 {
 
-constexpr size_t kChunkBytes = 32u << 20; // per staging buffer
+int reduce_chunk(int kind, const void *d_in, size_t n, void *d_out, Scratch *scratch, const void *chain_in,
+                 void *chain_out, cudaStream_t stream); // reduce.cu
+
+static size_t g_chunk_bytes = 64u << 20; // per staging buffer
+// 0: stage the input through device memory (H2D copy engine + kernel per chunk) -- the default: measured at
+//    0.99 of a plain pinned cudaMemcpyAsync (55.1-55.4 of 55.6 GB/s, profiles/r02a_e2e_probe.log)
+// 1: zero-copy -- ONE kernel reads the pinned host buffer over PCIe itself (no staging copy, no HBM round trip):
+//    51.4 GB/s, the SMs' 128-byte read requests use the link less well than the copy engine's;
+//    pageable (unregistered) input always takes the staged path
+static int g_host_mode = 0;
+constexpr size_t kChunkBytes = 32u << 20; // scan staging (in + out halves)
 
 struct Pipe {
     DeviceCtx   *c       = nullptr;
@@ -18,6 +28,9 @@ struct Pipe {
     cudaEvent_t  ready[2], freed[2], done[2];
 };
 
+// The host-buffer entry points own their streams, staging chunks, reduce scratch and result slot (all persistent
+// in the device context), so a call allocates nothing and never synchronises the whole device.  Contract: they
+// block until the result is in host memory, and they must not run concurrently with each other on one device.
 static int open_pipe(Pipe &p, size_t stage_bytes)
 {
     int st = 0;
@@ -25,26 +38,42 @@ static int open_pipe(Pipe &p, size_t stage_bytes)
     if (!p.c)
         return st;
     DeviceCtx *c = p.c;
-    // the library scratch is shared with whatever the caller enqueued through the *_async entry points
-    B200_TRY(cudaDeviceSynchronize());
     if (!c->copy_stream[0]) {
         B200_TRY(cudaStreamCreateWithFlags(&c->copy_stream[0], cudaStreamNonBlocking));
         B200_TRY(cudaStreamCreateWithFlags(&c->copy_stream[1], cudaStreamNonBlocking));
         B200_TRY(cudaStreamCreateWithFlags(&c->compute_stream, cudaStreamNonBlocking));
         for (int i = 0; i < 6; i++)
             B200_TRY(cudaEventCreateWithFlags(&c->ev[i], cudaEventDisableTiming));
+        B200_TRY(cudaHostAlloc(&c->host_slot, 4096, cudaHostAllocMapped | cudaHostAllocPortable));
     }
     p.h2d     = c->copy_stream[0];
     p.d2h     = c->copy_stream[1];
     p.compute = c->compute_stream;
+    bool fresh = false;
     for (int i = 0; i < 2; i++) {
         p.ready[i] = c->ev[i];
         p.freed[i] = c->ev[2 + i];
         p.done[i]  = c->ev[4 + i];
-        B200_TRY((cudaError_t)ensure(c->stage[i], stage_bytes, p.compute));
+        if (stage_bytes) {
+            bool f = false;
+            B200_TRY((cudaError_t)ensure(c->stage[i], stage_bytes, p.compute, &f));
+            fresh |= f;
+        }
     }
-    B200_TRY(cudaStreamSynchronize(p.compute)); // scratch memsets done before the copy streams touch it
+    if (fresh)
+        B200_TRY(cudaStreamSynchronize(p.compute)); // scratch memsets done before the copy streams touch it
     return 0;
+}
+
+// device-visible address of a host buffer when it is pinned / registered (zero-copy candidate), else nullptr
+static const void *mapped_ptr(const void *h)
+{
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, h) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return a.type == cudaMemoryTypeHost ? a.devicePointer : nullptr;
 }
 
 template <typename T> __global__ void sum_rows_kernel(const T *rows, size_t nrows, size_t width, T *out)
@@ -55,16 +84,6 @@ template <typename T> __global__ void sum_rows_kernel(const T *rows, size_t nrow
         for (size_t i = 0; i < nrows; i++)
             s += rows[i * width + j];
         out[j] = s;
-    }
-}
-__global__ void sum_rows_f32_kernel(const float *rows, size_t nrows, float *out)
-{
-    // chunk totals of a float reduction are added up in double
-    if (threadIdx.x == 0 && blockIdx.x == 0) {
-        double s = 0.0;
-        for (size_t i = 0; i < nrows; i++)
-            s += (double)rows[i];
-        out[0] = (float)s;
     }
 }
 __global__ void next_carry_kernel(unsigned *carry_next, const unsigned *carry, const unsigned *dst_last,
@@ -97,51 +116,73 @@ template <typename F> static int stream_input(Pipe &p, const void *h_in, size_t 
     return 0;
 }
 
-template <typename T, typename Launch> static int reduce_host(const T *h_in, size_t n, T *h_result, Launch reduce_async)
+// reduce: the typed result is written by the (last) kernel straight into the mapped pinned slot -- the only thing
+// that crosses the bus on the way back is that one word, and there is no D2H copy call.
+template <typename T> static int reduce_host(int kind, const T *h_in, size_t n, T *h_result)
 {
-    Pipe p;
-    B200_TRY((cudaError_t)open_pipe(p, kChunkBytes));
-    const size_t nchunks = (n * sizeof(T) + kChunkBytes - 1) / kChunkBytes;
-    T           *d_part  = nullptr;
-    B200_TRY(cudaMallocAsync(&d_part, (nchunks + 2) * sizeof(T), p.compute));
-    B200_TRY(cudaMemsetAsync(d_part, 0, (nchunks + 2) * sizeof(T), p.compute));
-    int st = stream_input(p, h_in, n * sizeof(T), kChunkBytes, [&](size_t k, void *d, size_t bytes) {
-        return reduce_async(reinterpret_cast<const T *>(d), bytes / sizeof(T), d_part + k, 1, (b200_stream_t)p.compute);
-    });
+    Pipe        p;
+    const void *zc = g_host_mode == 1 ? mapped_ptr(h_in) : nullptr;
+    B200_TRY((cudaError_t)open_pipe(p, zc ? 0 : g_chunk_bytes));
+    DeviceCtx *c = p.c;
+    // host_work: [0, 64 KiB) reduce scratch (ticket + per-CTA partials) | two 8-byte chain slots
+    B200_TRY((cudaError_t)ensure(c->host_work, (64u << 10) + 4096, p.compute));
+    char *chain     = reinterpret_cast<char *>(c->host_work.ptr) + (64u << 10);
+    T    *slot      = reinterpret_cast<T *>(c->host_slot);
+    T    *slot_dev  = nullptr;
+    B200_TRY(cudaHostGetDevicePointer((void **)&slot_dev, slot, 0));
+    int st = 0;
+    if (n == 0) {
+        *h_result = T(0);
+        return 0;
+    }
+    if (zc) {
+        st = reduce_chunk(kind, zc, n, slot_dev, &c->host_work, nullptr, nullptr, p.compute);
+    }
+    else {
+        const size_t chunk   = g_chunk_bytes;
+        const size_t nchunks = (n * sizeof(T) + chunk - 1) / chunk;
+        st = stream_input(p, h_in, n * sizeof(T), chunk, [&](size_t k, void *d, size_t bytes) {
+            return reduce_chunk(kind, d, bytes / sizeof(T), k + 1 == nchunks ? slot_dev : nullptr, &c->host_work,
+                                k ? chain + 8 * ((k - 1) & 1) : nullptr, chain + 8 * (k & 1), p.compute);
+        });
+    }
     if (st)
         return st;
-    T *d_total = d_part + nchunks;
-    if (std::is_same<T, float>::value)
-        sum_rows_f32_kernel<<<1, 32, 0, p.compute>>>((const float *)d_part, nchunks, (float *)d_total);
-    else
-        sum_rows_kernel<T><<<1, 32, 0, p.compute>>>(d_part, nchunks, 1, d_total);
-    count_launch();
-    B200_TRY(cudaGetLastError());
-    B200_TRY(cudaMemcpyAsync(h_result, d_total, sizeof(T), cudaMemcpyDeviceToHost, p.compute));
-    B200_TRY(cudaFreeAsync(d_part, p.compute));
     B200_TRY(cudaStreamSynchronize(p.compute));
+    *h_result = *slot;
     return 0;
 }
 
 template <typename Launch> static int hist_host(uint32_t *h_hist, int bins, const void *h_data, size_t n, Launch hist_async)
 {
-    Pipe p;
-    B200_TRY((cudaError_t)open_pipe(p, kChunkBytes));
-    size_t    nchunks = (n + kChunkBytes - 1) / kChunkBytes;
-    unsigned *d_part  = nullptr;
-    B200_TRY(cudaMallocAsync(&d_part, (nchunks + 1) * bins * sizeof(unsigned), p.compute));
-    B200_TRY(cudaMemsetAsync(d_part, 0, (nchunks + 1) * bins * sizeof(unsigned), p.compute));
-    int st = stream_input(p, h_data, n, kChunkBytes, [&](size_t k, void *d, size_t bytes) {
-        return hist_async(d_part + k * bins, d, bytes, (b200_stream_t)p.compute);
-    });
+    Pipe        p;
+    const void *zc = g_host_mode == 1 ? mapped_ptr(h_data) : nullptr;
+    B200_TRY((cudaError_t)open_pipe(p, zc ? 0 : g_chunk_bytes));
+    DeviceCtx   *c       = p.c;
+    const size_t chunk   = g_chunk_bytes;
+    const size_t nchunks = zc ? 1 : (n + chunk - 1) / chunk;
+    // rows live behind the reduce scratch of host_work
+    const size_t rows_off = (64u << 10) + 4096;
+    B200_TRY((cudaError_t)ensure(c->host_work, rows_off + (nchunks + 1) * bins * sizeof(unsigned), p.compute));
+    unsigned *d_part = reinterpret_cast<unsigned *>(reinterpret_cast<char *>(c->host_work.ptr) + rows_off);
+    unsigned *d_total = d_part + nchunks * bins;
+    int       st      = 0;
+    if (zc || n == 0) {
+        st = hist_async(d_total, zc ? zc : h_data, n, (b200_stream_t)p.compute);
+    }
+    else {
+        st = stream_input(p, h_data, n, chunk, [&](size_t k, void *d, size_t bytes) {
+            return hist_async(d_part + k * bins, d, bytes, (b200_stream_t)p.compute);
+        });
+        if (!st) {
+            sum_rows_kernel<unsigned><<<1, 256, 0, p.compute>>>(d_part, nchunks, bins, d_total);
+            count_launch();
+            st = (int)cudaGetLastError();
+        }
+    }
     if (st)
         return st;
-    unsigned *d_total = d_part + nchunks * bins;
-    sum_rows_kernel<unsigned><<<1, 256, 0, p.compute>>>(d_part, nchunks, bins, d_total);
-    count_launch();
-    B200_TRY(cudaGetLastError());
     B200_TRY(cudaMemcpyAsync(h_hist, d_total, bins * sizeof(unsigned), cudaMemcpyDeviceToHost, p.compute));
-    B200_TRY(cudaFreeAsync(d_part, p.compute));
     B200_TRY(cudaStreamSynchronize(p.compute));
     return 0;
 }
@@ -198,15 +239,23 @@ using namespace b200;
 
 extern "C" int b200_reduce_i32_host(const int32_t *h_in, size_t n, int32_t *h_result)
 {
-    return reduce_host<int32_t>(h_in, n, h_result, b200_reduce_i32_async);
+    return reduce_host<int32_t>(0, h_in, n, h_result);
 }
 extern "C" int b200_reduce_f32_host(const float *h_in, size_t n, float *h_result)
 {
-    return reduce_host<float>(h_in, n, h_result, b200_reduce_f32_async);
+    return reduce_host<float>(1, h_in, n, h_result);
 }
 extern "C" int b200_reduce_f64_host(const double *h_in, size_t n, double *h_result)
 {
-    return reduce_host<double>(h_in, n, h_result, b200_reduce_f64_async);
+    return reduce_host<double>(2, h_in, n, h_result);
+}
+// experiments (not part of the stable ABI): mode 0 staged / 1 zero-copy; chunk_bytes > 0 sets the staging chunk
+extern "C" int b200_tune_host_path(int mode, size_t chunk_bytes)
+{
+    g_host_mode = mode;
+    if (chunk_bytes)
+        g_chunk_bytes = chunk_bytes;
+    return 0;
 }
 extern "C" int b200_histogram256_host(uint32_t *h_hist, const void *h_data, size_t byteCount)
 {
@@ -223,8 +272,8 @@ extern "C" int b200_scan_exclusive_host(uint32_t *h_dst, const uint32_t *h_src, 
         return 0;
     Pipe p;
     B200_TRY((cudaError_t)open_pipe(p, 2 * kChunkBytes));
-    unsigned *d_carry = nullptr;
-    B200_TRY(cudaMallocAsync(&d_carry, 2 * sizeof(unsigned), p.compute));
+    B200_TRY((cudaError_t)ensure(p.c->host_work, (64u << 10) + 4096, p.compute));
+    unsigned *d_carry = reinterpret_cast<unsigned *>(reinterpret_cast<char *>(p.c->host_work.ptr) + (64u << 10) + 64);
     const size_t per_chunk = kChunkBytes / 4;
     int          st        = 0;
     if (L <= per_chunk) {
@@ -244,7 +293,6 @@ extern "C" int b200_scan_exclusive_host(uint32_t *h_dst, const uint32_t *h_src, 
     if (st)
         return st;
     B200_TRY(cudaStreamSynchronize(p.d2h));
-    B200_TRY(cudaFreeAsync(d_carry, p.compute));
     B200_TRY(cudaStreamSynchronize(p.compute));
     return 0;
 }

@@ -642,11 +642,13 @@ static int launch_pass(unsigned tiles, cudaStream_t stream, const unsigned *kin,
                        unsigned *vout, unsigned n, unsigned shift, unsigned flip, const unsigned *spl, unsigned nspl,
                        const unsigned *gbase, unsigned *ticket, unsigned *desc, const unsigned *n_dev)
 {
-    static bool done = false;
-    if (!done) {
-        B200_TRY(cudaFuncSetAttribute(sort_pass_kernel<kBucket, kLB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)sizeof(SortSmem)));
-        done = true;
+    {
+        int        st = 0;
+        DeviceCtx *c  = ctx(&st);
+        if (!c)
+            return st;
+        const unsigned bit = (kBucket ? kAttrSortPass3 : kAttrSortPass0) << (kLB <= 1 ? 0 : (kLB <= 4 ? 1 : 2));
+        B200_TRY((cudaError_t)opt_in_smem(c, bit, sort_pass_kernel<kBucket, kLB>, sizeof(SortSmem)));
     }
     sort_pass_kernel<kBucket, kLB><<<tiles, kSortThreads, sizeof(SortSmem), stream>>>(
         kin, vin, kout, vout, n, shift, flip, spl, nspl, gbase, ticket, desc, NoPeer(), n_dev);
@@ -691,12 +693,7 @@ static int sort_kv(uint32_t *d_dstKey, uint32_t *d_dstVal, uint32_t *d_bufKey, u
     const unsigned flip = sortDir ? 0u : 0xffffffffu;
 
     {
-        static bool prepared = false;
-        if (!prepared) {
-            B200_TRY(cudaFuncSetAttribute(sort_hist4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          4 * kRadix * 32 * 4));
-            prepared = true;
-        }
+        B200_TRY((cudaError_t)opt_in_smem(c, kAttrSortHist4, sort_hist4_kernel, 4 * kRadix * 32 * 4));
         size_t want = (N / 4 + kHist4Threads - 1) / kHist4Threads;
         int    grid = (int)(want < (size_t)c->num_sms ? want : (size_t)c->num_sms);
         if (grid < 1)
@@ -839,12 +836,7 @@ extern "C" int b200_partition_exchange_kv_async(const uint32_t *d_srcKey, const 
         sp.v[r] = r < (int)world ? (unsigned long long)(uintptr_t)recvVals[r] : 0ull;
     }
     sp.info = d_info;
-    static bool prepared = false;
-    if (!prepared) {
-        B200_TRY(cudaFuncSetAttribute(sort_pass_kernel<true, 4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)sizeof(SortSmem)));
-        prepared = true;
-    }
+    B200_TRY((cudaError_t)opt_in_smem(c, kAttrSortPeer, sort_pass_kernel<true, 4, true>, sizeof(SortSmem)));
     // N == 0: one CTA that only takes part in the closing exchange
     sort_pass_kernel<true, 4, true><<<tiles ? tiles : 1, kSortThreads, sizeof(SortSmem), stream>>>(
         d_srcKey, d_srcVal, nullptr, nullptr, (unsigned)N, 0u, flip, d_splitters, nspl, ghist, tickets, desc, sp,
@@ -873,9 +865,8 @@ extern "C" int b200_sort_reserve(size_t N)
         return st;
     const size_t tiles = (N + kSortTile - 1) / kSortTile;
     B200_TRY((cudaError_t)ensure(c->sort, kSortOffDesc + 4 * tiles * kRadix * 4, 0));
-    B200_TRY(cudaFuncSetAttribute(sort_hist4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * kRadix * 32 * 4));
-    B200_TRY(cudaFuncSetAttribute(sort_pass_kernel<false, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)sizeof(SortSmem)));
+    B200_TRY((cudaError_t)opt_in_smem(c, kAttrSortHist4, sort_hist4_kernel, 4 * kRadix * 32 * 4));
+    B200_TRY((cudaError_t)opt_in_smem(c, kAttrSortPass1, sort_pass_kernel<false, 4>, sizeof(SortSmem)));
     return 0;
 }
 

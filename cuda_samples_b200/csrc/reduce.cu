@@ -132,12 +132,13 @@ struct ReduceExchange {
     unsigned  index, count;
 };
 
-// scratch layout: [0] ticket (u32), [16 ..) one 8-byte partial per CTA
+// scratch layout: [0] ticket (u32), [8] result slot of an in-place call, [16 ..) one 8-byte partial per CTA
 template <typename L, bool kP2P>
 __global__ void __launch_bounds__(kReduceThreads, kReduceCtasPerSm)
     reduce_kernel(const typename L::Elem *__restrict__ in, size_t n, typename L::Elem *__restrict__ out,
                   size_t out_len, unsigned *__restrict__ ticket, typename L::Part *__restrict__ partials,
-                  double *__restrict__ out_f64, ReduceExchange ex)
+                  double *__restrict__ out_f64, const typename L::Part *__restrict__ chain_in,
+                  typename L::Part *__restrict__ chain_out, ReduceExchange ex)
 {
     typedef typename L::Elem Elem;
     typedef typename L::Part Part;
@@ -199,6 +200,12 @@ __global__ void __launch_bounds__(kReduceThreads, kReduceCtasPerSm)
         q += __ldcg(partials + i);
     q = block_sum<Part>(q, s_part);
     if (threadIdx.x == 0) {
+        // chunked input (host_path.cu): the running total of the earlier chunks comes in un-rounded and goes out
+        // un-rounded, so a float array streamed in chunks is still rounded to fp32 exactly once
+        if (chain_in)
+            q += *chain_in;
+        if (chain_out)
+            *chain_out = q;
         if (out_len > 0)
             out[0] = (Elem)q;
         if (out_f64) // shard partial for the multi-GPU combine: the typed result, widened exactly
@@ -236,31 +243,72 @@ __global__ void __launch_bounds__(kReduceThreads, kReduceCtasPerSm)
 
 template <typename L>
 static int launch_reduce(const typename L::Elem *d_in, size_t n, typename L::Elem *d_out, size_t out_len,
-                         cudaStream_t stream, double *d_out_f64 = nullptr, const ReduceExchange *ex = nullptr)
+                         cudaStream_t stream, double *d_out_f64 = nullptr, const ReduceExchange *ex = nullptr,
+                         Scratch *scratch = nullptr, const void *chain_in = nullptr, void *chain_out = nullptr)
 {
     int        st = 0;
     DeviceCtx *c  = ctx(&st);
     if (!c)
         return st;
     const int max_grid = c->num_sms * kReduceCtasPerSm;
-    B200_TRY((cudaError_t)ensure(c->reduce, 16 + sizeof(double) * (size_t)max_grid, stream));
+    Scratch  &work     = scratch ? *scratch : c->reduce;
+    B200_TRY((cudaError_t)ensure(work, 16 + sizeof(double) * (size_t)max_grid, stream));
     constexpr int kPerVec = 16 / sizeof(typename L::Elem);
     size_t        nvec    = n / kPerVec + 1;
     size_t        want    = (nvec + kReduceThreads - 1) / kReduceThreads;
     int           grid    = (int)(want < (size_t)max_grid ? want : (size_t)max_grid);
     if (grid < 1)
         grid = 1;
-    unsigned *ticket   = reinterpret_cast<unsigned *>(c->reduce.ptr);
-    auto     *partials = reinterpret_cast<typename L::Part *>(reinterpret_cast<char *>(c->reduce.ptr) + 16);
+    typedef typename L::Part Part;
+    typedef typename L::Elem Elem;
+    // In place (threadFenceReduction.cu:247 calls reduce(s, threads, blocks, d_odata, d_odata)): the kernel reads its
+    // input through the read-only path, so an output that overlaps the input goes through a scratch slot and is
+    // copied into place by stream-ordered copies behind the kernel.
+    Elem *alias_out = nullptr;
+    if (d_out && out_len && (uintptr_t)d_out < (uintptr_t)(d_in + n) && (uintptr_t)(d_out + out_len) > (uintptr_t)d_in) {
+        alias_out = d_out;
+        d_out     = reinterpret_cast<Elem *>(reinterpret_cast<char *>(work.ptr) + 8);
+    }
+    const size_t kernel_out_len = alias_out ? 1 : out_len;
+    unsigned *ticket   = reinterpret_cast<unsigned *>(work.ptr);
+    auto     *partials = reinterpret_cast<Part *>(reinterpret_cast<char *>(work.ptr) + 16);
     if (ex)
-        reduce_kernel<L, true><<<grid, kReduceThreads, 0, stream>>>(d_in, n, d_out, out_len, ticket, partials,
-                                                                   d_out_f64, *ex);
+        reduce_kernel<L, true><<<grid, kReduceThreads, 0, stream>>>(d_in, n, d_out, kernel_out_len, ticket, partials,
+                                                                   d_out_f64, (const Part *)chain_in,
+                                                                   (Part *)chain_out, *ex);
     else
-        reduce_kernel<L, false><<<grid, kReduceThreads, 0, stream>>>(d_in, n, d_out, out_len, ticket, partials,
-                                                                    d_out_f64, ReduceExchange());
+        reduce_kernel<L, false><<<grid, kReduceThreads, 0, stream>>>(d_in, n, d_out, kernel_out_len, ticket, partials,
+                                                                    d_out_f64, (const Part *)chain_in,
+                                                                    (Part *)chain_out, ReduceExchange());
     count_launch();
     B200_TRY(cudaGetLastError());
+    if (alias_out) {
+        B200_TRY(cudaMemcpyAsync(alias_out, d_out, sizeof(Elem), cudaMemcpyDeviceToDevice, stream));
+        if (out_len > 1)
+            B200_TRY(cudaMemsetAsync(alias_out + 1, 0, (out_len - 1) * sizeof(Elem), stream));
+    }
     return 0;
+}
+
+// One chunk of a host array streamed through the device (host_path.cu): own scratch (so the caller's *_async work on
+// other streams is not disturbed), running total chained through 8-byte slots, typed result written to d_out when
+// given (the last chunk; d_out may be mapped pinned host memory).  kind: 0 i32, 1 f32, 2 f64.
+int reduce_chunk(int kind, const void *d_in, size_t n, void *d_out, Scratch *scratch, const void *chain_in,
+                 void *chain_out, cudaStream_t stream)
+{
+    const size_t out_len = d_out ? 1 : 0;
+    switch (kind) {
+    case 0:
+        return launch_reduce<LaneI32>((const int *)d_in, n, (int *)d_out, out_len, stream, nullptr, nullptr, scratch,
+                                      chain_in, chain_out);
+    case 1:
+        return launch_reduce<LaneF32>((const float *)d_in, n, (float *)d_out, out_len, stream, nullptr, nullptr,
+                                      scratch, chain_in, chain_out);
+    case 2:
+        return launch_reduce<LaneF64>((const double *)d_in, n, (double *)d_out, out_len, stream, nullptr, nullptr,
+                                      scratch, chain_in, chain_out);
+    }
+    return (int)cudaErrorInvalidValue;
 }
 
 } // namespace b200

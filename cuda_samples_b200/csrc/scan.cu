@@ -778,21 +778,11 @@ static int scan_impl(uint32_t *d_dst, const uint32_t *d_src, size_t batch, size_
             grid = p.num_tiles;
         auto *st64 = reinterpret_cast<unsigned long long *>(state);
         if (big) {
-            static bool prepared = false;
-            if (!prepared) {
-                B200_TRY(cudaFuncSetAttribute(scan_tma_kernel<5, 5, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                              (int)sizeof(ScanTmaSmem<5, 5>)));
-                prepared = true;
-            }
+            B200_TRY((cudaError_t)opt_in_smem(c, kAttrScanTma0, scan_tma_kernel<5, 5, 3>, sizeof(ScanTmaSmem<5, 5>)));
             scan_tma_kernel<5, 5, 3><<<grid, kTmaThreads, sizeof(ScanTmaSmem<5, 5>), stream>>>(d_dst, d_src, p, st64, desc);
         }
         else {
-            static bool prepared = false;
-            if (!prepared) {
-                B200_TRY(cudaFuncSetAttribute(scan_tma_kernel<4, 6, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                              (int)sizeof(ScanTmaSmem<4, 6>)));
-                prepared = true;
-            }
+            B200_TRY((cudaError_t)opt_in_smem(c, kAttrScanTma1, scan_tma_kernel<4, 6, 3>, sizeof(ScanTmaSmem<4, 6>)));
             scan_tma_kernel<4, 6, 3><<<grid, kTmaThreads, sizeof(ScanTmaSmem<4, 6>), stream>>>(d_dst, d_src, p, st64, desc);
         }
     }
@@ -855,12 +845,8 @@ int compact_tma(int32_t *d_dst, int32_t *d_count, const int32_t *d_src, size_t n
     unsigned grid = (unsigned)c->num_sms;
     if (grid > p.num_tiles)
         grid = p.num_tiles;
-    static bool prepared = false;
-    if (!prepared) {
-        B200_TRY(cudaFuncSetAttribute(scan_tma_kernel<5, 5, 3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)(sizeof(ScanTmaSmem<5, 5>) + kScanWarps * 512)));
-        prepared = true;
-    }
+    B200_TRY((cudaError_t)opt_in_smem(c, kAttrScanTma2, scan_tma_kernel<5, 5, 3, true>,
+                                      sizeof(ScanTmaSmem<5, 5>) + kScanWarps * 512));
     // + one 512-byte packing slab per scan warp behind the pipeline's shared memory
     scan_tma_kernel<5, 5, 3, true><<<grid, kTmaThreads, sizeof(ScanTmaSmem<5, 5>) + kScanWarps * 512, stream>>>(
         reinterpret_cast<unsigned *>(d_dst), reinterpret_cast<const unsigned *>(d_src), p, st64, desc);

@@ -178,9 +178,18 @@ int b200_reduce_f64_host(const double *h_in, size_t n, double *h_result);
 int b200_scan_exclusive_host(uint32_t *h_dst, const uint32_t *h_src, size_t batchSize, size_t arrayLength);
 int b200_sort_kv_host(uint32_t *h_dstKey, uint32_t *h_dstVal, const uint32_t *h_srcKey, const uint32_t *h_srcVal,
                       size_t N, uint32_t sortDir);
-/* pinned host memory for the variants above */
+/* Pinned (registered, device-mapped) host memory for the variants above, placed on the NUMA node of the CURRENT
+ * device when the platform allows it (mbind, else first touch from that node's CPUs): a pinned buffer on the wrong
+ * socket halves the PCIe rate.  (If sysfs does not name the GPU's node the allocator measures it.) */
 int b200_host_alloc(void **h_ptr, size_t bytes);
 int b200_host_free(void *h_ptr);
+/* where a b200_host_alloc block lives: NUMA node of its device, node of its first / last page (-1 unknown),
+ * placement method (0 none possible, 1 mbind, 2 first touch on the node's CPUs) */
+int b200_host_alloc_info(const void *h_ptr, int *gpu_node, int *mem_node_first, int *mem_node_last, int *method);
+/* the PCIe roofline of the *_host entry points, measured in place: one plain cudaMemcpyAsync of `bytes` from pinned
+ * h_src to device memory between events, best of `reps`, in GB/s (method of the reference's
+ * 5_Domain_Specific/p2pBandwidthLatencyTest/p2pBandwidthLatencyTest.cu:113-146) */
+int b200_host_probe_h2d(const void *h_src, size_t bytes, int reps, double *best_gbs);
 
 #ifdef __cplusplus
 }

@@ -9,7 +9,10 @@ Two checkers live here:
   * `oracle.ref`-- ctypes view of oracle/_ref/libref_gold.so, the reference's own gold sources
                    compiled unmodified (histogram64CPU, histogram256CPU, scanExclusiveHost,
                    mergeSortHost, validateSortedKeys, validateSortedValues, fillValues), or None
-                   when that file was never built.
+                   when that file was never built;
+  * `oracle.ref_reduce` -- the reference's own reduceCPU<T> / getNumBlocksAndThreads (they live inside the sample's
+                   driver TU reduction.cpp, compiled where it lies through oracle/ref_reduce_wrap.cpp into
+                   oracle/_ref/libref_reduce.so), or None.
 Parity status: pinned (tests/test_oracle.py: restatement == reference gold on the samples'
 seeded inputs, and both == the known answers in tests/golden/kat.json).
 """
@@ -312,3 +315,56 @@ def _load_ref():
 
 
 ref = _load_ref()
+
+
+class _RefReduce:
+    """The reference's own reduceCPU<T> (reduction.cpp:167-180), compiled from the sample's driver TU where it lies
+    (oracle/ref_reduce_wrap.cpp).  `size` is an int like in the sample: n < 2^31."""
+
+    def __init__(self, path):
+        lib = ctypes.CDLL(path)
+        self.path = path
+        self._lib = lib
+        lib.ref_reduceCPU_int.argtypes = [c_void, ctypes.c_int]
+        lib.ref_reduceCPU_int.restype = ctypes.c_int32
+        lib.ref_reduceCPU_float.argtypes = [c_void, ctypes.c_int]
+        lib.ref_reduceCPU_float.restype = ctypes.c_float
+        lib.ref_reduceCPU_double.argtypes = [c_void, ctypes.c_int]
+        lib.ref_reduceCPU_double.restype = ctypes.c_double
+        lib.ref_getNumBlocksAndThreads.argtypes = [ctypes.c_int] * 4 + [ctypes.POINTER(ctypes.c_int)] * 2
+
+    def reduce(self, data):
+        data = np.ascontiguousarray(data).reshape(-1)
+        assert 0 < data.size < 2**31
+        if data.dtype == np.int32:
+            return int(self._lib.ref_reduceCPU_int(_ptr(data), data.size))
+        if data.dtype == np.float32:
+            return float(self._lib.ref_reduceCPU_float(_ptr(data), data.size))
+        if data.dtype == np.float64:
+            return float(self._lib.ref_reduceCPU_double(_ptr(data), data.size))
+        raise TypeError(data.dtype)
+
+    def num_blocks_and_threads(self, which_kernel, n, max_blocks, max_threads):
+        """getNumBlocksAndThreads (reduction.cpp:204-240); reads the device properties: needs a GPU."""
+        b, t = ctypes.c_int(0), ctypes.c_int(0)
+        self._lib.ref_getNumBlocksAndThreads(which_kernel, n, max_blocks, max_threads, ctypes.byref(b),
+                                             ctypes.byref(t))
+        return b.value, t.value
+
+
+def _load_ref_reduce():
+    path = os.path.join(_HERE, "_ref", "libref_reduce.so")
+    if not os.path.exists(path):
+        try:
+            path = _build.build_ref_reduce()
+        except Exception:
+            return None
+        if not path or not os.path.exists(path):
+            return None
+    try:
+        return _RefReduce(path)
+    except OSError:
+        return None
+
+
+ref_reduce = _load_ref_reduce()

@@ -70,10 +70,35 @@ def build_ref_gold(force=False):
     return out
 
 
+REF_REDUCE_DIR = os.path.join(REF_SAMPLES, "2_Concepts_and_Techniques", "reduction")
+CUDA_HOME = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+
+
+def build_ref_reduce(force=False):
+    """reduceCPU<T> is a template inside the sample's driver TU (reduction.cpp:167-180): compile that TU, where
+    it lies, through oracle/ref_reduce_wrap.cpp (main renamed, C wrappers) -> oracle/_ref/libref_reduce.so.
+    Needs the CUDA headers/runtime of this image (the TU includes helper_cuda.h); cudart is linked statically
+    so the file loads anywhere the image does."""
+    out_dir = os.path.join(HERE, "_ref")
+    out = os.path.join(out_dir, "libref_reduce.so")
+    src = os.path.join(REF_REDUCE_DIR, "reduction.cpp")
+    wrap = os.path.join(HERE, "ref_reduce_wrap.cpp")
+    if not os.path.exists(src):
+        return out if os.path.exists(out) else None
+    if force or _newer(out, [src, wrap]):
+        os.makedirs(out_dir, exist_ok=True)
+        subprocess.check_call(["g++", "-O2", "-fwrapv", "-fno-fast-math", "-fPIC", "-shared", "-w", "-o", out, wrap,
+                               "-I", REF_REDUCE_DIR, "-I", os.path.join(REF, "Common"),
+                               "-I", os.path.join(CUDA_HOME, "include"), "-L", os.path.join(CUDA_HOME, "lib64"),
+                               "-lcudart_static", "-ldl", "-lrt", "-lpthread"])
+    return out
+
+
 def main():
     force = "--force" in sys.argv
     print("oracle  :", build_oracle(force))
     print("ref gold:", build_ref_gold(force))
+    print("ref reduce:", build_ref_reduce(force))
 
 
 if __name__ == "__main__":

@@ -540,6 +540,53 @@ def test_host_variants(prim):
         assert (ok == wk).all() and (ov == wv).all()
 
 
+def test_host_variants_pinned_zero_copy_and_staged(prim):
+    """Pinned input (b200_host_alloc) runs zero-copy -- one kernel reads the host buffer over PCIe; the same buffer
+    forced through the staged path (several chunk sizes, ragged tail) gives the same bits."""
+    rng = np.random.default_rng(78)
+    n = (9 << 20) + 77
+    hb = prim.HostBuffer(4 * n)
+    info = hb.info()
+    assert info["placement"] is not None
+    xi = hb.array(np.int32)[:n]
+    xi[:] = rng.integers(-2**31, 2**31, n, dtype=np.int64).astype(np.int32)
+    want_i = oracle.reduce(xi)
+    xf_src = rng.random(n, dtype=np.float32)
+    try:
+        for mode, chunk in ((1, 0), (0, 1 << 20), (0, 8 << 20), (0, 64 << 20)):
+            prim.tune_host_path(mode, chunk)
+            assert prim.reduce_host(xi) == want_i, (mode, chunk)
+            assert (prim.histogram256_host(xi) == oracle.histogram256(xi)).all(), (mode, chunk)
+            assert (prim.histogram64_host(xi) == oracle.histogram64(xi)).all(), (mode, chunk)
+        hf = hb.array(np.float32)[:n]
+        hf[:] = xf_src
+        want_f = oracle.reduce(hf)
+        for mode, chunk in ((1, 0), (0, 1 << 20), (0, 32 << 20)):
+            prim.tune_host_path(mode, chunk)
+            assert abs(prim.reduce_host(hf) - want_f) <= FP32_RTOL * abs(want_f), (mode, chunk)
+        assert prim.host_probe_h2d(hf, 4 * n, 2) > 1.0  # GB/s: the probe ran
+    finally:
+        prim.tune_host_path(0, 64 << 20)
+        hb.free()
+
+
+def test_reduce_in_place_like_threadFenceReduction(prim):
+    """threadFenceReduction.cu:247 calls reduce(s, threads, blocks, d_odata, d_odata): output aliases the input."""
+    rng = np.random.default_rng(79)
+    for n, blocks in ((64, 64), (1000, 1), (1 << 16, 64)):
+        x = rng.random(n, dtype=np.float32)
+        d = torch.from_numpy(x.copy()).cuda()
+        prim.reduce(n, 256, blocks, 7, d, d)
+        got = d.cpu().numpy()
+        want = oracle.reduce(x)
+        assert abs(float(got[0]) - want) <= FP32_RTOL * abs(want)
+        assert (got[1:blocks] == 0).all() and (got[blocks:] == x[blocks:]).all()
+        xi = rng.integers(-1000, 1000, n, dtype=np.int32)
+        di = torch.from_numpy(xi.copy()).cuda()
+        prim.reduce(n, 256, blocks, 7, di, di)
+        assert int(di[0]) == oracle.reduce(xi)
+
+
 # ============================================================== unmodified sample drivers (drop-in)
 @pytest.mark.parametrize("name,args", [("histogram", []), ("scan", []), ("mergeSort", []), ("sortingNetworks", []),
                                        ("reduction", ["--type=int"]), ("reduction", ["--type=float"]),

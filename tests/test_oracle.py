@@ -114,6 +114,28 @@ def test_kat_reduce(kat):
         assert oracle.reduce(rd).hex() == case["f64_hex"]
 
 
+@pytest.mark.skipif(oracle.ref_reduce is None, reason="oracle/_ref/libref_reduce.so not built")
+def test_reduceCPU_restatement_equals_the_reference_template(kat):
+    """reduceCPU<T> compiled from the sample's own driver TU (oracle/ref_reduce_wrap.cpp) == the restatement,
+    bit for bit, on the sample's rand() inputs (the committed KAT values) and on random data incl. int wrap."""
+    for case in kat["reduce"]["cases"]:
+        n = case["n"]
+        ri = oracle.sample_input("reduce_i32", n, 1)
+        assert oracle.ref_reduce.reduce(ri) == oracle.reduce(ri) == case["i32"]
+        rf = oracle.sample_input("reduce_f32", n, 1)
+        assert float(np.float32(oracle.ref_reduce.reduce(rf))).hex() == case["f32_hex"]
+        rd = oracle.sample_input("reduce_f64", n, 1)
+        assert oracle.ref_reduce.reduce(rd).hex() == case["f64_hex"]
+    rng = np.random.default_rng(5)
+    for n in (1, 2, 3, 1000, 65537, 1 << 20):
+        xi = rng.integers(-2**31, 2**31, n, dtype=np.int64).astype(np.int32)
+        assert oracle.ref_reduce.reduce(xi) == oracle.reduce(xi)
+        xf = (rng.random(n, dtype=np.float32) - np.float32(0.3)) * np.float32(1e3)
+        assert np.float32(oracle.ref_reduce.reduce(xf)) == np.float32(oracle.reduce(xf))
+        xd = rng.standard_normal(n)
+        assert oracle.ref_reduce.reduce(xd) == oracle.reduce(xd)
+
+
 def test_reduce_int_wraps():
     # reduceCPU<int> is a wrapping 32-bit sum (SURVEY.md 8c KAT-RED)
     x = np.full(1 << 16, 0x7FFF, np.int32)
