@@ -63,6 +63,24 @@ SIGNATURES = {
     "b200_p2p_buffer_free": (ci, [vp]),
     "b200_partition_exchange_kv_async": (ci, [vp, vp, sz, vp, u32, ctypes.POINTER(vp), ctypes.POINTER(vp), sz, vp, vp,
                                               vp]),
+    "b200_scan_reserve": (ci, [sz]),
+    "b200_sort_reserve": (ci, [sz]),
+    "b200_p2p_set_timeout_ms": (ci, [ctypes.c_uint]),
+    "b200_p2p_probe_store": (ci, [vp, vp, sz, ci, ci, ctypes.POINTER(ctypes.c_double), vp]),
+    "b200_sort_splitters_async": (ci, [vp, sz, u32, vp, vp]),
+    "b200_ctx_create": (ci, [ci, ctypes.POINTER(ci), ctypes.POINTER(vp)]),
+    "b200_ctx_destroy": (ci, [vp]),
+    "b200_ctx_num_devices": (ci, [vp]),
+    "b200_ctx_stream": (ci, [vp, ci, ctypes.POINTER(vp)]),
+    "b200_ctx_synchronize": (ci, [vp]),
+    "b200_histogram_sharded": (ci, [vp, ctypes.POINTER(vp), ctypes.POINTER(vp), ctypes.POINTER(vp),
+                                    ctypes.POINTER(sz)]),
+    "b200_reduce_sharded_i32": (ci, [vp, ctypes.POINTER(vp), ctypes.POINTER(sz), vp]),
+    "b200_reduce_sharded_f32": (ci, [vp, ctypes.POINTER(vp), ctypes.POINTER(sz), vp]),
+    "b200_reduce_sharded_f64": (ci, [vp, ctypes.POINTER(vp), ctypes.POINTER(sz), vp]),
+    "b200_scan_exclusive_sharded": (ci, [vp, ctypes.POINTER(vp), ctypes.POINTER(vp), ctypes.POINTER(sz)]),
+    "b200_sort_kv_sharded": (ci, [vp, ctypes.POINTER(vp), ctypes.POINTER(vp), sz, ctypes.POINTER(vp),
+                                  ctypes.POINTER(vp), ctypes.POINTER(sz), u32, ctypes.POINTER(sz)]),
     "b200_host_alloc": (ci, [ctypes.POINTER(vp), sz]),
     "b200_host_free": (ci, [vp]),
     "b200_host_alloc_info": (ci, [vp] + [ctypes.POINTER(ci)] * 4),

@@ -403,3 +403,89 @@ def host_probe_h2d(h_src, nbytes, reps=5):
 def tune_host_path(mode, chunk_bytes=0):
     """Experiments only: mode 0 = staged through device chunks, 1 = zero-copy for pinned input (default)."""
     check(lib.b200_tune_host_path(mode, chunk_bytes), "b200_tune_host_path")
+
+
+# -------------------------------------------- sharded primitives, ONE process driving all devices (C ABI)
+class ShardedContext:
+    """b200_ctx: peer access + exchange windows + one stream per device, created once; the sharded entry points take
+    one buffer per device.  Thin ctypes mirror of include/b200prim.h (csrc/sharded.cu); buffers are CUDA tensors (or
+    integer device pointers) living on the matching device."""
+
+    def __init__(self, devices):
+        self.devices = list(devices)
+        arr = (ctypes.c_int * len(self.devices))(*self.devices)
+        h = ctypes.c_void_p(0)
+        check(lib.b200_ctx_create(len(self.devices), arr, ctypes.byref(h)), "b200_ctx_create")
+        self.handle = h
+
+    def _ptrs(self, bufs):
+        assert len(bufs) == len(self.devices)
+        return (ctypes.c_void_p * len(bufs))(*[_dptr(b).value or 0 if b is not None else 0 for b in bufs])
+
+    def _sizes(self, ns):
+        assert len(ns) == len(self.devices)
+        return (ctypes.c_size_t * len(ns))(*[int(n) for n in ns])
+
+    def synchronize(self):
+        check(lib.b200_ctx_synchronize(self.handle), "b200_ctx_synchronize")
+
+    def histogram(self, hist256, hist64, data, nbytes):
+        check(lib.b200_histogram_sharded(self.handle, self._ptrs(hist256), self._ptrs(hist64), self._ptrs(data),
+                                         self._sizes(nbytes)), "b200_histogram_sharded")
+
+    def reduce(self, xs, ns):
+        kind = _REDUCE.get(str(xs[0].dtype))
+        out = np.zeros(1, {"i32": np.int32, "f32": np.float32, "f64": np.float64}[kind])
+        check(getattr(lib, "b200_reduce_sharded_%s" % kind)(self.handle, self._ptrs(xs), self._sizes(ns), _hptr(out)),
+              "b200_reduce_sharded_%s" % kind)
+        return out[0].item()
+
+    def scan_exclusive(self, dsts, srcs, ns):
+        check(lib.b200_scan_exclusive_sharded(self.handle, self._ptrs(dsts), self._ptrs(srcs), self._sizes(ns)),
+              "b200_scan_exclusive_sharded")
+
+    def sort_kv(self, dst_keys, dst_vals, capacity, src_keys, src_vals, ns, direction=1):
+        """-> list of pairs received per device; raises B200Error (status 2) when `capacity` is too small."""
+        n_out = (ctypes.c_size_t * len(self.devices))()
+        check(lib.b200_sort_kv_sharded(self.handle, self._ptrs(dst_keys), self._ptrs(dst_vals), capacity,
+                                       self._ptrs(src_keys), self._ptrs(src_vals), self._sizes(ns), direction, n_out),
+              "b200_sort_kv_sharded")
+        return [int(x) for x in n_out]
+
+    def destroy(self):
+        if self.handle:
+            check(lib.b200_ctx_destroy(self.handle), "b200_ctx_destroy")
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.destroy()
+        except Exception:
+            pass
+
+
+def sort_splitters(srcKey, N, sortDir, d_splitters, stream=None):
+    """Splitters of the sharded sort chosen on the device (one peer-window exchange); every rank must call it."""
+    check(lib.b200_sort_splitters_async(_dptr(srcKey), N, sortDir, _dptr(d_splitters), _stream(stream)),
+          "sort_splitters")
+
+
+def scan_reserve(n):
+    check(lib.b200_scan_reserve(n), "b200_scan_reserve")
+
+
+def sort_reserve(n):
+    check(lib.b200_sort_reserve(n), "b200_sort_reserve")
+
+
+def p2p_probe_store(d_dst, d_src, nbytes, mode, reps=5, stream=None):
+    """GB/s of writing nbytes from d_src (local) into d_dst (peer-mapped or local): mode 0 4-byte lane stores,
+    1 16-byte lane stores, 2 cp.async.bulk from shared memory, 3 cudaMemcpyAsync."""
+    g = ctypes.c_double(0.0)
+    check(lib.b200_p2p_probe_store(_dptr(d_dst), _dptr(d_src), nbytes, mode, reps, ctypes.byref(g), _stream(stream)),
+          "b200_p2p_probe_store")
+    return float(g.value)
+
+
+def p2p_set_timeout_ms(ms):
+    check(lib.b200_p2p_set_timeout_ms(ms), "b200_p2p_set_timeout_ms")

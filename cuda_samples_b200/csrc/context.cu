@@ -52,8 +52,16 @@ int ensure(Scratch &s, size_t bytes, cudaStream_t stream, bool *fresh)
         *fresh = false;
     if (s.bytes >= bytes)
         return 0;
-    // grow-only and rare (sizes settle after the first call): cudaFree synchronises the device, so
-    // work already enqueued on the old block has finished before it goes away.
+    // Growing is rare (sizes settle after the first call; init*() / b200_*_reserve pre-size) and it is the one place
+    // where an *_async entry point is not asynchronous: cudaFree synchronises the device (work enqueued on the old
+    // block has finished before it goes away) and the zero-fill is waited for, so that launches on ANY stream --
+    // also cudaStreamNonBlocking ones that do not order against the stream passed here -- see zeroed tickets and
+    // epochs.  That cannot be done inside a stream capture: fail with a status instead of breaking the capture.
+    if (stream != nullptr && stream != cudaStreamLegacy && stream != cudaStreamPerThread) {
+        cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+        if (cudaStreamIsCapturing(stream, &cs) == cudaSuccess && cs != cudaStreamCaptureStatusNone)
+            return (int)cudaErrorStreamCaptureUnsupported;
+    }
     if (s.ptr)
         B200_TRY(cudaFree(s.ptr));
     s.ptr   = nullptr;
@@ -61,6 +69,7 @@ int ensure(Scratch &s, size_t bytes, cudaStream_t stream, bool *fresh)
     size_t want = bytes < 4096 ? 4096 : bytes;
     B200_TRY(cudaMalloc(&s.ptr, want));
     B200_TRY(cudaMemsetAsync(s.ptr, 0, want, stream));
+    B200_TRY(cudaStreamSynchronize(stream));
     s.bytes = want;
     if (fresh)
         *fresh = true;
@@ -111,6 +120,25 @@ extern "C" int b200_device_info(int *num_sms, int *smem_optin, int *cc_major, in
 
 extern "C" unsigned long long b200_launch_count(void) { return g_launches.load(); }
 
+// what close*() of one primitive gives back: only that primitive's scratch (which: 0 histogram, 1 scan, 2 sort,
+// 3 reduce); the other primitives' state stays
+extern "C" int b200_release_scratch_of(int which)
+{
+    int        st = 0;
+    DeviceCtx *c  = ctx(&st);
+    if (!c)
+        return st;
+    B200_TRY(cudaDeviceSynchronize());
+    switch (which) {
+    case 0: release(c->hist); break;
+    case 1: release(c->scan); break;
+    case 2: release(c->sort); break;
+    case 3: release(c->reduce); break;
+    default: return (int)cudaErrorInvalidValue;
+    }
+    return 0;
+}
+
 extern "C" int b200_release_scratch(void)
 {
     int        st = 0;
@@ -125,5 +153,6 @@ extern "C" int b200_release_scratch(void)
     release(c->image);
     release(c->stage[0]);
     release(c->stage[1]);
+    release(c->host_work);
     return 0;
 }

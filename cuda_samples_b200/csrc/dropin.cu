@@ -32,8 +32,10 @@ void initHistogram256(void)
     if (!b200::ctx(&st))
         B200_OR_DIE(st, "initHistogram256");
 }
-void closeHistogram64(void) { B200_OR_DIE(b200_release_scratch(), "closeHistogram64"); }
-void closeHistogram256(void) { B200_OR_DIE(b200_release_scratch(), "closeHistogram256"); }
+// close*() of one primitive frees that primitive's scratch only (the samples' close* free their own buffer:
+// histogram256.cu:141-143, scan.cu:189, mergeSort.cu:463-469)
+void closeHistogram64(void) { B200_OR_DIE(b200_release_scratch_of(0), "closeHistogram64"); }
+void closeHistogram256(void) { B200_OR_DIE(b200_release_scratch_of(0), "closeHistogram256"); }
 
 void histogram64(uint *d_Histogram, void *d_Data, uint byteCount)
 {
@@ -58,7 +60,7 @@ void initScan(void)
     // the sample allocates its scratch here (scan.cu:184-187); pre-size ours for MAX_BATCH_ELEMENTS
     B200_OR_DIE(b200_scan_reserve(64u * 1048576u), "initScan");
 }
-void closeScan(void) { B200_OR_DIE(b200_release_scratch(), "closeScan"); }
+void closeScan(void) { B200_OR_DIE(b200_release_scratch_of(1), "closeScan"); }
 
 size_t scanExclusiveShort(uint *d_Dst, uint *d_Src, uint batchSize, uint arrayLength)
 {
@@ -77,7 +79,7 @@ void initMergeSort(void)
     // the sample allocates its scratch here (mergeSort.cu:455-461); pre-size ours for its maximum N = 2^22
     B200_OR_DIE(b200_sort_reserve(4u * 1048576u), "initMergeSort");
 }
-void closeMergeSort(void) { B200_OR_DIE(b200_release_scratch(), "closeMergeSort"); }
+void closeMergeSort(void) { B200_OR_DIE(b200_release_scratch_of(2), "closeMergeSort"); }
 
 void mergeSort(uint *dstKey, uint *dstVal, uint *bufKey, uint *bufVal, uint *srcKey, uint *srcVal, uint N,
                uint sortDir)

@@ -295,6 +295,18 @@ static int launch_hist(unsigned *out256, unsigned *out64, const void *d_data, si
     return 0;
 }
 
+int hist_preload()
+{
+    cudaFuncAttributes fa;
+    B200_TRY(cudaFuncGetAttributes(&fa, histogram_kernel<kHistFusedP2P>));
+    B200_TRY(cudaFuncGetAttributes(&fa, histogram_kernel<kHistFused>));
+    int        st = 0;
+    DeviceCtx *c  = ctx(&st);
+    if (!c)
+        return st;
+    return ensure(c->hist, kHistWords * sizeof(unsigned), 0);
+}
+
 int set_hist_cluster(int cluster)
 {
     if (cluster != 0 && cluster != 1 && cluster != 2 && cluster != 4 && cluster != 8)

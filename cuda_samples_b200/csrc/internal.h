@@ -6,6 +6,7 @@
 
 extern "C" int b200_sort_reserve(size_t N);
 extern "C" int b200_scan_reserve(size_t n);
+extern "C" int b200_release_scratch_of(int which);
 
 namespace b200 {
 extern std::atomic<unsigned long long> g_launches;

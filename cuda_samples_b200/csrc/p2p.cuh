@@ -26,11 +26,12 @@ constexpr unsigned kP2PSlotWords = 512;              // u32 payload words per ra
 constexpr unsigned kP2PSlotBytes = 4 * kP2PSlotWords; // payload bytes
 constexpr unsigned kP2PHeaderBytes = 64;
 constexpr size_t   kP2PWindowBytes = kP2PHeaderBytes + 2ull * kP2PMaxRanks * kP2PSlotWords * 8;
-constexpr unsigned long long kP2PTimeoutNs = 10ull * 1000 * 1000 * 1000;
+constexpr unsigned long long kP2PTimeoutNs = 30ull * 1000 * 1000 * 1000; // default; b200_p2p_set_timeout_ms changes it
 
 struct P2PArgs { // kernel parameter, by value
     unsigned long long win[kP2PMaxRanks]; // device addresses of all windows (own one included), 0 beyond world
     unsigned           rank, world;
+    unsigned long long timeout_ns;        // bounded wait for a peer's word
 };
 
 __device__ __forceinline__ unsigned long long *p2p_slot(unsigned long long win, unsigned parity, unsigned src)
@@ -87,7 +88,10 @@ __device__ __forceinline__ unsigned p2p_peer_word(const P2PArgs &a, unsigned seq
         const unsigned long long t0 = p2p_now();
         do {
             v = ld_sys_u64(p);
-            if (p2p_now() - t0 > kP2PTimeoutNs) { // b200_p2p_errors(): a peer never arrived; this call's results are void
+            if (p2p_now() - t0 > a.timeout_ns) {
+                // A peer never arrived: this call's results are void.  The count is STICKY (never reset while the
+                // windows live) and every host-side wrapper that synchronises checks it and fails loudly
+                // (b200_p2p_errors; the b200_*_sharded entry points return cudaErrorLaunchTimeout).
                 atomicAdd(reinterpret_cast<unsigned long long *>(a.win[a.rank]) + 1, 1ull);
                 break;
             }
@@ -99,5 +103,8 @@ __device__ __forceinline__ unsigned p2p_peer_word(const P2PArgs &a, unsigned seq
 // host side (p2p.cu): the connected window set of the current device, or world == 0 when b200_p2p_connect() has
 // not been called
 const P2PArgs *p2p_args();
+// ONE process driving all devices (sharded.cu): windows are plain cudaMalloc'ed blocks reached through peer access
+int p2p_connect_local(int ndev, const int *devices);
+int p2p_disconnect_local(int ndev, const int *devices);
 
 } // namespace b200

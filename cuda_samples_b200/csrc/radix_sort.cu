@@ -36,14 +36,24 @@ namespace b200 {
 #endif
 constexpr int      kSortThreads = B200_SORT_THREADS;
 constexpr int      kSortWarps   = kSortThreads / 32;
-constexpr int      kSortItems   = B200_SORT_ITEMS;
+constexpr int      kSortItems   = B200_SORT_ITEMS;     // pairs per thread
 constexpr int      kSortCtasPerSm = B200_SORT_CTAS;
-constexpr unsigned kSortTile    = kSortThreads * kSortItems; // pairs per tile (4096)
-static_assert(kSortThreads >= 256 && kSortTile <= 65536, "digit owners are threads 0..255; rank | digit << 16");
+constexpr unsigned kSortTile    = kSortThreads * kSortItems; // pairs per tile (8192)
+static_assert(kSortThreads >= 256 && kSortTile <= 65536, "digit owners are threads 0..255; 16-bit slots");
 constexpr int      kRadix       = 256;
-#ifndef B200_SORT_RANK_MODE
-#define B200_SORT_RANK_MODE 0 // 0: the group's lowest lane bumps the digit counter with ATOMS.ADD; 1: with LDS + STS
+#ifndef B200_SORT_PACKED
+#define B200_SORT_PACKED 1 // 1: (key, value) staged as ONE 64-bit word per pair (one STS.64 from inside the ranking
+                           //    loop, one LDS.64 in the store phase); 0: keys and values staged separately
 #endif
+#ifndef B200_SORT_VALS_EARLY
+#define B200_SORT_VALS_EARLY (B200_SORT_PACKED ? B200_SORT_ITEMS : 8) // values whose loads precede the ranking loop
+#endif
+#ifndef B200_SORT_LB_FIRST
+#define B200_SORT_LB_FIRST 0 // 1: the look-back runs BEFORE the ranking loop (prefix published ~5 us earlier: shorter
+                             //    chains for every successor, but this tile waits for it up front)
+#endif
+constexpr int      kValsEarly = B200_SORT_VALS_EARLY;
+static_assert(!B200_SORT_PACKED || kValsEarly == kSortItems, "packed staging needs every value before the ranking loop");
 constexpr unsigned kDescA = 1u << 30, kDescP = 2u << 30, kDescValue = (1u << 30) - 1;
 
 #ifdef B200_SCAN_TRACE
@@ -63,11 +73,16 @@ __device__ __forceinline__ unsigned long long sort_now()
 
 // shared memory of the pass kernel (dynamic)
 struct SortSmem {
+#if B200_SORT_PACKED
+    uint2    pair[kSortTile];             // (key, value) in digit order
+#else
     unsigned buf[kSortTile];              // keys in digit order
     unsigned vbuf[kSortTile];             // values in digit order
-    unsigned wcnt[kSortWarps][kRadix];    // per warp and digit: running count while ranking, then the warp's
-                                          // tile-local scatter base for the digit (plain u32: all 32 banks)
+#endif
+    unsigned wcnt[kSortWarps][kRadix];    // per warp and digit: count, then the warp's running scatter position
     unsigned gofs[kRadix];                // global index of a digit's first slot minus its tile-local start
+    unsigned cnt[kRadix];                 // parking space (tile count / tile-local start per digit) while the
+    unsigned tstart[kRadix];              //   ranking loop needs every register
     unsigned wsum[kRadix / 32];
     unsigned splitters[kRadix];
     unsigned tile;
@@ -134,6 +149,21 @@ __device__ __forceinline__ unsigned match_digit(unsigned d)
     match_bit<6>(mask, d);
     match_bit<7>(mask, d);
     return mask;
+}
+
+__device__ __forceinline__ uint4 ld_relaxed_v4(const unsigned *p)
+{
+    uint4 r;
+    asm volatile("ld.relaxed.gpu.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p)
+                 : "memory");
+    return r;
+}
+__device__ __forceinline__ void st_relaxed_v4(unsigned *p, uint4 v)
+{
+    asm volatile("st.relaxed.gpu.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+                 : "memory");
 }
 
 // Last CTA of a histogram kernel: warp p turns histogram p (256 counts) into exclusive offsets in place
@@ -377,20 +407,20 @@ __global__ void __launch_bounds__(kHist4Threads, 1)
 }
 
 // ---------------------------------------------------------------------------------------------------
-// One scatter pass (chained scan over tiles).
-// What bounds this kernel is the SM's load/store data pipe (ncu: l1tex__data_pipe_lsu_wavefronts at 82 % of
-// peak in the first version, issue slots at 33 %), so the kernel is written to spend as few shared/global
-// WAVEFRONTS per pair as possible and pays for that with ALU work:
-//   * ranking inside a warp: the lanes holding the same digit are found with eight vote.ballot (registers only);
-//     the group's lowest lane then bumps a warp-private u32 counter with ONE shared atomic that returns the
-//     count so far (the first version used a 64-bit {mask, count} word per digit: an ATOMS.OR, a 64-bit load
-//     and a 64-bit store per item on 16 of the 32 banks);
-//   * rank = count so far + number of lower lanes in the mask.  Index order inside the tile = (warp, item, lane),
-//     so ranks are stable;
-//   * the per-digit sweep over the warps reads the eight counters once, keeps them in registers across the
-//     block scan and writes the eight scatter bases once;
-//   * keys go to shared memory as soon as the bases are known; the values are loaded only then (their latency
-//     hides behind the look-back), so that at most 32 payload registers are live and nothing spills.
+// One scatter pass (chained scan over tiles).  Measured limits (ncu + per-tile traces, profiles/r02*): the pass is
+// bound by SM-side work per pair and by phases that wait -- not by DRAM (36 %).  Round 1 ranked first and published
+// the tile's digit counts afterwards; 24 % of all warp stall samples sat at barriers, 16 % at the one that waits for
+// the look-back.  Order of a tile now:
+//   1. keys in (warp-striped), then ONE shared RED per key on the warp's private digit row ("early counts");
+//   2. the digit owners (threads 0..255) add the warps' counts and PUBLISH the tile aggregate right away (~4 us
+//      earlier than before: every successor's look-back finds it already there), scan the 256 counts and turn the
+//      rows into running scatter positions;
+//   3. ranking: eight vote.ballot per key find the lanes with the same digit (registers only), the group's lowest
+//      lane bumps the warp's scatter position with one shared atomic, and the (key, value) pair goes straight to its
+//      tile-local slot as one 64-bit store -- no rank array, no second staging loop;
+//   4. look-back by the digit owners (kLB descriptor rows per round trip), inclusive prefix published;
+//   5. every digit's run leaves as contiguous stores.
+// Index order inside the tile = (warp, item, lane): ranks are stable by construction.
 // ---------------------------------------------------------------------------------------------------
 template <bool kBucket, int kLB, bool kPeer = false>
 __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
@@ -431,10 +461,11 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
     const bool       full  = valid == kSortTile;
     DigitOp<kBucket> op{shift, flip, nspl, S.splitters};
 
-    // ---- load keys (warp-striped: item i of lane l is element warp*(items*32) + i*32 + l of the tile) ----
+    // ---- 1. keys (warp-striped: item i of lane l is element warp*(items*32) + i*32 + l of the tile), early counts --
     unsigned       key[kSortItems];
     const unsigned wbase = warp * (kSortItems * 32) + lane;
     const unsigned pad   = ~flip; // (pad ^ flip) = 0xffffffff: last digit in every pass, ranks after all valid keys
+    unsigned      *mycnt = S.wcnt[warp];
     if (full) {
 #pragma unroll
         for (int i = 0; i < kSortItems; i++)
@@ -445,165 +476,192 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
         for (int i = 0; i < kSortItems; i++)
             key[i] = (wbase + i * 32 < valid) ? __ldg(kin + base + wbase + i * 32) : pad;
     }
-
-    // ---- rank inside the warp, in index order ------------------------------------------------------------
-    unsigned  rank[kSortItems]; // rank | digit << 16
-    unsigned *mycnt = S.wcnt[warp];
 #ifdef B200_SCAN_TRACE
     if (key[kSortItems - 1] == 0x12345678u)
         SORT_TRACE(tile, 7); // (forces the last key load to complete before slot 1 is stamped)
     SORT_TRACE(tile, 1);
 #endif
+    unsigned dig[kBucket ? kSortItems / 4 : 1]; // bucket digits (a binary search each) are computed once and kept
+    if (kBucket) {
+#pragma unroll
+        for (int i = 0; i < kSortItems / 4; i++)
+            dig[i] = 0;
+    }
 #pragma unroll
     for (int i = 0; i < kSortItems; i++) {
-        const unsigned d     = op(key[i]);
-        const unsigned mask  = match_digit(d);
-        const unsigned below = mask & lt;
-        unsigned       pre   = 0;
-        if (below == 0) {
-#if B200_SORT_RANK_MODE == 1
-            pre      = mycnt[d]; // groups of one round hold distinct digits: no atomicity needed inside a warp
-            mycnt[d] = pre + __popc(mask);
-#else
-            pre = atomicAdd(mycnt + d, (unsigned)__popc(mask));
-#endif
-        }
-        pre     = __shfl_sync(0xffffffffu, pre, __ffs(mask) - 1);
-        rank[i] = (pre + __popc(below)) | (d << 16);
-#if B200_SORT_RANK_MODE == 1
-        __syncwarp();
-#endif
+        const unsigned d = op(key[i]);
+        if (kBucket)
+            dig[i / 4] |= d << (8 * (i & 3));
+        atomicAdd(mycnt + d, 1u);
     }
     SORT_TRACE(tile, 2);
     __syncthreads();
 
-    // ---- per digit: order the warps, publish the tile count, first look-back poll -----------------------
-    unsigned  count = 0, tile_start = 0;
-    unsigned  c[kSortWarps];
-    unsigned  first_poll[kLB];
-    long long t_back = (long long)tile - 1;
-    if (tid < kRadix) {
+    // ---- 2. per digit: add the warps' counts, publish the tile aggregate, scan, running scatter positions --------
+    {
+        unsigned count = 0, tile_start = 0;
+        unsigned c[kSortWarps];
+        if (tid < kRadix) {
 #pragma unroll
-        for (int w = 0; w < kSortWarps; w++) {
-            c[w] = S.wcnt[w][tid];
-            count += c[w];
+            for (int w = 0; w < kSortWarps; w++) {
+                c[w] = S.wcnt[w][tid];
+                count += c[w];
+            }
+            st_relaxed_u32(desc + (size_t)tile * kRadix + tid, (tile == 0 ? kDescP : kDescA) | count);
+            unsigned inc = count;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                unsigned t = __shfl_up_sync(0xffffffffu, inc, d);
+                if (lane >= d)
+                    inc += t;
+            }
+            if (lane == 31)
+                S.wsum[warp] = inc;
+            tile_start = inc - count;
         }
-        st_relaxed_u32(desc + (size_t)tile * kRadix + tid, (tile == 0 ? kDescP : kDescA) | count);
-        // issued now, consumed after the staging below (which needs only tile-local offsets)
-        if (tile > 0) {
+        SORT_TRACE(tile, 3);
+        __syncthreads();
+        if (tid < kRadix) {
 #pragma unroll
-            for (int j = 0; j < kLB; j++)
-                first_poll[j] = (t_back - j >= 0) ? ld_relaxed_u32(desc + tid + (size_t)(t_back - j) * kRadix) : kDescP;
-        }
-        // exclusive scan of the 256 counts -> where each digit starts inside the tile
-        unsigned inc = count;
+            for (int w = 0; w < kRadix / 32; w++)
+                tile_start += (w < (int)warp) ? S.wsum[w] : 0u;
+            unsigned run = tile_start;
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            unsigned t = __shfl_up_sync(0xffffffffu, inc, d);
-            if (lane >= d)
-                inc += t;
-        }
-        if (lane == 31)
-            S.wsum[warp] = inc;
-        tile_start = inc - count;
-    }
-    SORT_TRACE(tile, 3);
-    __syncthreads();
-    if (tid < kRadix) {
-#pragma unroll
-        for (int w = 0; w < kRadix / 32; w++)
-            tile_start += (w < (int)warp) ? S.wsum[w] : 0u;
-        unsigned run = tile_start;
-#pragma unroll
-        for (int w = 0; w < kSortWarps; w++) {
-            S.wcnt[w][tid] = run;
-            run += c[w];
+            for (int w = 0; w < kSortWarps; w++) {
+                S.wcnt[w][tid] = run;
+                run += c[w];
+            }
+            S.cnt[tid]    = count; // parked: the ranking loop needs every register
+            S.tstart[tid] = tile_start;
         }
     }
     __syncthreads();
 
-    // ---- keys to shared memory in digit order; the slot replaces the rank -----------------------------------
+    // look back: thread d walks over the earlier tiles' counts of digit d, kLB rows per round trip; publishes the
+    // inclusive prefix and leaves gofs[d] = global index of the digit's first slot minus its tile-local start
+    auto look_back = [&]() {
+        if (tid < kRadix) {
+            unsigned       excl  = 0;
+            const unsigned count = S.cnt[tid];
+            if (tile > 0) {
+                const unsigned *dp     = desc + tid;
+                long long       t_back = (long long)tile - 1;
+                bool            done   = false;
+#ifdef B200_SCAN_TRACE
+                unsigned polls = 0, stalls = 0;
+#endif
+                while (!done) {
+#ifdef B200_SCAN_TRACE
+                    polls++;
+#endif
+                    unsigned d[kLB];
+#pragma unroll
+                    for (int j = 0; j < kLB; j++)
+                        d[j] = (t_back - j >= 0) ? ld_relaxed_u32(dp + (size_t)(t_back - j) * kRadix) : kDescP;
+                    long long t = t_back;
+#pragma unroll
+                    for (int j = 0; j < kLB; j++) {
+                        if (done)
+                            break;
+                        if ((d[j] >> 30) == 0) {
+#ifdef B200_SCAN_TRACE
+                            stalls++;
+#endif
+                            break; // not published yet: poll again from this tile
+                        }
+                        excl += d[j] & kDescValue;
+                        t--;
+                        done = (d[j] & kDescP) != 0;
+                    }
+                    t_back = t;
+                }
+#ifdef B200_SCAN_TRACE
+                if (g_sort_trace && threadIdx.x == 0)
+                    g_sort_trace[(size_t)tile * 8 + 7] = ((unsigned long long)stalls << 32) | polls;
+#endif
+                st_relaxed_u32(desc + (size_t)tile * kRadix + tid, kDescP | (excl + count));
+            }
+            S.gofs[tid] = __ldg(gbase + tid) + excl - S.tstart[tid];
+            SORT_TRACE(tile, 4);
+        }
+    };
+#if B200_SORT_LB_FIRST
+    look_back();
+#endif
+
+    // ---- 3. values, then ranking: the pair goes straight to its tile-local slot ---------------------------------
+    unsigned val[kSortItems];
+    auto     load_vals = [&](int lo, int hi) {
+        if (full) {
+#pragma unroll
+            for (int i = lo; i < hi; i++)
+                val[i] = __ldg(vin + base + wbase + i * 32);
+        }
+        else {
+#pragma unroll
+            for (int i = lo; i < hi; i++)
+                val[i] = (wbase + i * 32 < valid) ? __ldg(vin + base + wbase + i * 32) : 0u;
+        }
+    };
+    load_vals(0, kValsEarly);
+#if !B200_SORT_PACKED
+    unsigned slot2[kSortItems / 2]; // two 16-bit slots per register
+#endif
 #pragma unroll
     for (int i = 0; i < kSortItems; i++) {
-        const unsigned slot = (rank[i] & 0xffffu) + mycnt[rank[i] >> 16]; // tile-local position
-        S.buf[slot]         = key[i];
-        rank[i]             = slot;
-    }
-    // ---- values: loaded now, in flight during the look-back ------------------------------------------------
-    unsigned val[kSortItems];
-    if (full) {
-#pragma unroll
-        for (int i = 0; i < kSortItems; i++)
-            val[i] = __ldg(vin + base + wbase + i * 32);
-    }
-    else {
-#pragma unroll
-        for (int i = 0; i < kSortItems; i++)
-            val[i] = (wbase + i * 32 < valid) ? __ldg(vin + base + wbase + i * 32) : 0u;
+        unsigned kk = key[i];
+        asm volatile("" : "+r"(kk)); // recompute the digit here: keeping 16 digits/addresses alive from the counting
+                                     // loop costs more registers than the two instructions that rebuild them
+        const unsigned d     = kBucket ? ((dig[i / 4] >> (8 * (i & 3))) & 255u) : op(kk);
+        const unsigned mask  = match_digit(d);
+        const unsigned below = mask & lt;
+        unsigned       pre   = 0;
+        if (below == 0)
+            pre = atomicAdd(mycnt + d, (unsigned)__popc(mask));
+        pre                 = __shfl_sync(0xffffffffu, pre, __ffs(mask) - 1);
+        const unsigned slot = pre + __popc(below);
+#if B200_SORT_PACKED
+        S.pair[slot] = make_uint2(kk, val[i]);
+#else
+        S.buf[slot] = kk;
+        if (i & 1)
+            slot2[i / 2] |= slot << 16;
+        else
+            slot2[i / 2] = slot;
+#endif
     }
     SORT_TRACE(tile, 6);
-
-    // ---- look back: thread d walks over the earlier tiles' counts of digit d, kLB rows per round trip ---------
-    if (tid < kRadix) {
-        unsigned excl = 0;
-        if (tile > 0) {
-            const unsigned *dp   = desc + tid;
-            bool            done = false, first = true;
-#ifdef B200_SCAN_TRACE
-            unsigned polls = 0, stalls = 0;
+#if !B200_SORT_PACKED
+    load_vals(kValsEarly, kSortItems);
 #endif
-            while (!done) {
-#ifdef B200_SCAN_TRACE
-                polls++;
+    // ---- 4. look-back ----------------------------------------------------------------------------------------
+#if !B200_SORT_LB_FIRST
+    look_back();
 #endif
-                unsigned d[kLB];
-#pragma unroll
-                for (int j = 0; j < kLB; j++)
-                    d[j] = first ? first_poll[j]
-                                 : ((t_back - j >= 0) ? ld_relaxed_u32(dp + (size_t)(t_back - j) * kRadix) : kDescP);
-                first = false;
-                long long t = t_back;
-#pragma unroll
-                for (int j = 0; j < kLB; j++) {
-                    if (done)
-                        break;
-                    if ((d[j] >> 30) == 0) {
-#ifdef B200_SCAN_TRACE
-                        stalls++;
-#endif
-                        break; // not published yet: poll again from this tile
-                    }
-                    excl += d[j] & kDescValue;
-                    t--;
-                    done = (d[j] & kDescP) != 0;
-                }
-                t_back = t;
-            }
-#ifdef B200_SCAN_TRACE
-            if (g_sort_trace && threadIdx.x == 0)
-                g_sort_trace[(size_t)tile * 8 + 7] = ((unsigned long long)stalls << 32) | polls;
-#endif
-            st_relaxed_u32(desc + (size_t)tile * kRadix + tid, kDescP | (excl + count));
-        }
-        S.gofs[tid] = __ldg(gbase + tid) + excl - tile_start;
-        SORT_TRACE(tile, 4);
-    }
+#if !B200_SORT_PACKED
 #pragma unroll
     for (int i = 0; i < kSortItems; i++)
-        S.vbuf[rank[i]] = val[i];
+        S.vbuf[(i & 1) ? slot2[i / 2] >> 16 : slot2[i / 2] & 0xffffu] = val[i];
+#endif
     __syncthreads();
     SORT_TRACE(tile, 5);
-    // ---- out: every digit's run leaves as contiguous stores ---------------------------------------------------
+    // ---- 5. out: every digit's run leaves as contiguous stores -------------------------------------------------
+#if B200_SORT_PACKED
+#define SORT_KEY_AT(j) S.pair[j].x
+#define SORT_PAIR_AT(j) const uint2 pr = S.pair[j]; const unsigned x = pr.x, y = pr.y
+#else
+#define SORT_PAIR_AT(j) const unsigned x = S.buf[j], y = S.vbuf[j]
+#endif
     if constexpr (kPeer) {
 #pragma unroll
         for (int k = 0; k < kSortItems; k++) {
             const unsigned j = tid + k * kSortThreads;
-            const unsigned x = S.buf[j];
+            SORT_PAIR_AT(j);
             const unsigned d = op(x); // bucket == destination rank
             const unsigned g = S.gofs[d] + j;
             if (j < valid) {
                 reinterpret_cast<unsigned *>(peer.k[d])[g] = x;
-                reinterpret_cast<unsigned *>(peer.v[d])[g] = S.vbuf[j];
+                reinterpret_cast<unsigned *>(peer.v[d])[g] = y;
             }
         }
     }
@@ -611,24 +669,71 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
 #pragma unroll
         for (int k = 0; k < kSortItems; k++) {
             const unsigned j = tid + k * kSortThreads;
-            const unsigned x = S.buf[j];
+            SORT_PAIR_AT(j);
             const unsigned g = S.gofs[op(x)] + j;
             kout[g]          = x;
-            vout[g]          = S.vbuf[j];
+            vout[g]          = y;
         }
     }
     else {
 #pragma unroll
         for (int k = 0; k < kSortItems; k++) {
             const unsigned j = tid + k * kSortThreads;
-            const unsigned x = S.buf[j];
+            SORT_PAIR_AT(j);
             const unsigned g = S.gofs[op(x)] + j;
             if (j < valid) {
                 kout[g] = x;
-                vout[g] = S.vbuf[j];
+                vout[g] = y;
             }
         }
     }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Splitters of the multi-GPU sample sort, chosen on the device with no collective call: every rank takes 512
+// regular samples of its keys (in ordered space: key ^ flip), the samples are exchanged through the peer windows
+// (512 words = one slot), every rank sorts the same world x 512 samples with a bitonic network in shared memory
+// and keeps samples [b * 512], b = 1 .. world-1 -- the same choice on every rank, with no host round trip.
+// ---------------------------------------------------------------------------------------------------
+constexpr unsigned kSplitSamples = kP2PSlotWords; // 512
+constexpr int      kSplitThreads = 1024;
+__global__ void __launch_bounds__(kSplitThreads, 1)
+    sort_splitters_kernel(P2PArgs a, const unsigned *__restrict__ keys, unsigned n, unsigned flip,
+                          unsigned *__restrict__ splitters /* world-1, ascending, ordered space */)
+{
+    __shared__ unsigned           s_own[kSplitSamples];
+    __shared__ unsigned           s_all[kP2PMaxRanks * kSplitSamples]; // 32 KiB
+    __shared__ unsigned long long s_seq;
+    const unsigned                step = n / kSplitSamples > 0 ? n / kSplitSamples : 1;
+    for (unsigned i = threadIdx.x; i < kSplitSamples; i += kSplitThreads) {
+        const unsigned long long idx = (unsigned long long)i * step;
+        s_own[i] = n ? (keys[idx < n ? idx : n - 1] ^ flip) : 0xffffffffu; // an empty shard votes for "high"
+    }
+    __syncthreads();
+    const unsigned seq   = p2p_exchange(a, s_own, kSplitSamples, &s_seq);
+    const unsigned total = a.world * kSplitSamples;
+    unsigned       pow2  = 1;
+    while (pow2 < total)
+        pow2 <<= 1;
+    for (unsigned i = threadIdx.x; i < pow2; i += kSplitThreads)
+        s_all[i] = i < total ? p2p_peer_word(a, seq, i / kSplitSamples, i % kSplitSamples) : 0xffffffffu;
+    __syncthreads();
+    for (unsigned k = 2; k <= pow2; k <<= 1)
+        for (unsigned j = k >> 1; j > 0; j >>= 1) {
+            for (unsigned i = threadIdx.x; i < pow2; i += kSplitThreads) {
+                const unsigned p = i ^ j;
+                if (p > i) {
+                    const unsigned x = s_all[i], y = s_all[p];
+                    if (((i & k) == 0) == (x > y)) {
+                        s_all[i] = y;
+                        s_all[p] = x;
+                    }
+                }
+            }
+            __syncthreads();
+        }
+    if (threadIdx.x + 1 < a.world)
+        splitters[threadIdx.x] = s_all[(threadIdx.x + 1) * kSplitSamples];
 }
 
 // scratch layout (bytes): [0,16) hist ticket | [16, 16+4 KiB) digit offsets [4][256]
@@ -869,6 +974,43 @@ extern "C" int b200_sort_reserve(size_t N)
     B200_TRY((cudaError_t)opt_in_smem(c, kAttrSortPass1, sort_pass_kernel<false, 4>, sizeof(SortSmem)));
     return 0;
 }
+
+// Splitters of the sharded sort on the device (b200_p2p_connect / b200_ctx_create first): d_splitters receives
+// world-1 ascending values in ordered key space (key for ascending sorts, ~key for descending), identical on every
+// rank.  Every rank must call it (it contains one exchange).
+extern "C" int b200_sort_splitters_async(const uint32_t *d_srcKey, size_t N, uint32_t sortDir, uint32_t *d_splitters,
+                                         b200_stream_t stream)
+{
+    const P2PArgs *a = p2p_args();
+    if (!a || a->world < 1 || N >= (1ull << 32))
+        return (int)cudaErrorInvalidValue;
+    sort_splitters_kernel<<<1, kSplitThreads, 0, (cudaStream_t)stream>>>(*a, d_srcKey, (unsigned)N,
+                                                                       sortDir ? 0u : 0xffffffffu, d_splitters);
+    count_launch();
+    B200_TRY(cudaGetLastError());
+    return 0;
+}
+
+namespace b200 {
+// load every kernel of the sharded sort onto the current device and opt in to its shared memory, so that nothing
+// but launches happens once kernels start waiting for each other (sharded.cu)
+int sort_preload()
+{
+    int        st = 0;
+    DeviceCtx *c  = ctx(&st);
+    if (!c)
+        return st;
+    cudaFuncAttributes fa;
+    B200_TRY(cudaFuncGetAttributes(&fa, sort_splitters_kernel));
+    B200_TRY(cudaFuncGetAttributes(&fa, sort_hist_kernel<true, true>));
+    B200_TRY((cudaError_t)opt_in_smem(c, kAttrSortPeer, sort_pass_kernel<true, 4, true>, sizeof(SortSmem)));
+    B200_TRY((cudaError_t)opt_in_smem(c, kAttrSortHist4, sort_hist4_kernel, 4 * kRadix * 32 * 4));
+    B200_TRY((cudaError_t)opt_in_smem(c, kAttrSortPass1, sort_pass_kernel<false, 4>, sizeof(SortSmem)));
+    B200_TRY((cudaError_t)opt_in_smem(c, kAttrSortPass0, sort_pass_kernel<false, 1>, sizeof(SortSmem)));
+    B200_TRY((cudaError_t)opt_in_smem(c, kAttrSortPass2, sort_pass_kernel<false, 8>, sizeof(SortSmem)));
+    return 0;
+}
+} // namespace b200
 
 #ifdef B200_SCAN_TRACE
 extern "C" int b200_debug_set_sort_trace(void *d_trace)

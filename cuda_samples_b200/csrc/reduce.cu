@@ -290,6 +290,22 @@ static int launch_reduce(const typename L::Elem *d_in, size_t n, typename L::Ele
     return 0;
 }
 
+int reduce_preload()
+{
+    cudaFuncAttributes fa;
+    B200_TRY(cudaFuncGetAttributes(&fa, reduce_kernel<LaneI32, true>));
+    B200_TRY(cudaFuncGetAttributes(&fa, reduce_kernel<LaneF32, true>));
+    B200_TRY(cudaFuncGetAttributes(&fa, reduce_kernel<LaneF64, true>));
+    B200_TRY(cudaFuncGetAttributes(&fa, reduce_kernel<LaneI32, false>));
+    B200_TRY(cudaFuncGetAttributes(&fa, reduce_kernel<LaneF32, false>));
+    B200_TRY(cudaFuncGetAttributes(&fa, reduce_kernel<LaneF64, false>));
+    int        st = 0;
+    DeviceCtx *c  = ctx(&st);
+    if (!c)
+        return st;
+    return ensure(c->reduce, 16 + sizeof(double) * (size_t)c->num_sms * kReduceCtasPerSm, 0);
+}
+
 // One chunk of a host array streamed through the device (host_path.cu): own scratch (so the caller's *_async work on
 // other streams is not disturbed), running total chained through 8-byte slots, typed result written to d_out when
 // given (the last chunk; d_out may be mapped pinned host memory).  kind: 0 i32, 1 f32, 2 f64.

@@ -886,6 +886,22 @@ extern "C" int b200_scan_reserve(size_t n)
     return 0;
 }
 
+namespace b200 {
+int scan_preload()
+{
+    int        st = 0;
+    DeviceCtx *c  = ctx(&st);
+    if (!c)
+        return st;
+    B200_TRY((cudaError_t)opt_in_smem(c, kAttrScanTma0, scan_tma_kernel<5, 5, 3>, sizeof(ScanTmaSmem<5, 5>)));
+    B200_TRY((cudaError_t)opt_in_smem(c, kAttrScanTma1, scan_tma_kernel<4, 6, 3>, sizeof(ScanTmaSmem<4, 6>)));
+    cudaFuncAttributes fa;
+    B200_TRY(cudaFuncGetAttributes(&fa, scan_kernel<true>));
+    B200_TRY(cudaFuncGetAttributes(&fa, scan_kernel<false>));
+    return ensure(c->scan, 4096, 0);
+}
+} // namespace b200
+
 #ifdef B200_SCAN_TRACE
 extern "C" int b200_debug_set_scan_trace(void *d_trace)
 {

@@ -204,6 +204,7 @@ class PendingReduce:
     def typed(self):
         """-> list of python scalars in the inputs' own types (int: wrapped to int32 like reduceCPU<int>)."""
         vals = self.result().cpu().tolist()
+        check_p2p()
         out = []
         for v, dt in zip(vals, self.dtypes):
             if dt == torch.int32:
@@ -281,47 +282,71 @@ def choose_splitters(samples_ordered, world):
     return s[idx]
 
 
-def sort_sharded(keys, vals, n_local, direction=1, ops=None, group=None, samples_per_rank=1024, capacity_factor=1.25):
+def check_p2p():
+    """Raise if any fused exchange on this rank ever lost a peer (sticky device-side count, csrc/p2p.cuh): the results
+    of that call are void.  Synchronises the device."""
+    if p2p_enabled():
+        n = api.p2p_errors()
+        if n:
+            raise api.B200Error("NVLink peer-window exchange: %d word(s) never arrived within the timeout -- a rank "
+                                "is missing or lagging; results of the affected calls are void" % n)
+
+
+def sort_sharded(keys, vals, n_local, direction=1, ops=None, group=None, samples_per_rank=1024, capacity_factor=1.25,
+                 sync=True):
     """Stable global key-value sort.  Rank r ends up with the r-th key range (ascending ranges for
     direction=1, descending for 0).  -> (keys_out, vals_out, n_out, counts_matrix).
-    With enable_p2p() the partition pass stores every bucket straight into its destination rank's receive buffer
-    over NVLink (no all-to-all, no host round trip before the local sort); a receive buffer holds
-    capacity_factor x the largest shard, and a distribution that overflows it falls back to the NCCL path."""
+    With enable_p2p() nothing but kernels of libb200prim.so run: splitters are chosen on the device (samples exchanged
+    through the peer windows), the partition pass stores every bucket straight into its destination rank's receive
+    buffer over NVLink (no all-to-all, no host round trip before the local sort), the local sort reads its pair count
+    on the device.  A receive buffer holds capacity_factor x the largest shard; a distribution that overflows it falls
+    back to the NCCL path.  The output tensors of the p2p path belong to the library and are reused by the next call
+    with the same shard size.  sync=False (p2p path only) returns (keys_out, vals_out, meta, None) without any host
+    synchronisation: meta is the device tensor [world*world counts | pairs received | overflow flag]."""
     ops = ops or CudaOps()
     rank, world = _world(group)
     if world == 1:
         dk, dv = ops.sort(keys, vals, n_local, direction)
         return dk, dv, n_local, None
     flip = 0 if direction else 0xFFFFFFFF
-    # 1. regular samples of the local keys, in ordered space
-    ns = min(samples_per_rank, max(n_local, 1))
-    step = max(n_local // ns, 1)
-    local = _u32_as_i64(keys[:n_local:step][:ns]) ^ flip
-    if local.numel() < ns:  # tiny shards: pad by repetition so every rank contributes ns samples
-        pad = local[-1:].expand(ns - local.numel()) if local.numel() else torch.zeros(ns, dtype=torch.int64,
-                                                                                    device=keys.device)
-        local = torch.cat([local, pad])
-    gathered = torch.empty(world * ns, dtype=torch.int64, device=keys.device)
-    dist.all_gather_into_tensor(gathered, local.contiguous(), group=group)
-    spl64 = choose_splitters(gathered, world)
-    spl = torch.where(spl64 >= 2**31, spl64 - 2**32, spl64).to(torch.int32).contiguous()
+    spl = None
     if p2p_enabled() and isinstance(ops, CudaOps) and world == _P2P["world"]:
-        # 2-4 fused: count + exchange of counts, partition pass that scatters into the peers' receive buffers
         b = _recv_buffers(n_local, capacity_factor, rank, world, group)
         cap = b["capacity"]
-        meta = torch.empty(world * world + 2, dtype=torch.int32, device=keys.device)
+        if "work" not in b:  # per-shape work buffers live with the receive buffers: nothing is allocated per call
+            mk = lambda n: torch.empty(n, dtype=torch.int32, device=keys.device)  # noqa: E731
+            b["work"] = {"spl": mk(max(world - 1, 1)), "meta": mk(world * world + 2), "dk": mk(cap), "dv": mk(cap),
+                         "bk": mk(cap), "bv": mk(cap)}
+        w = b["work"]
+        spl, meta = w["spl"], w["meta"]
+        # 1. splitters on the device: regular samples -> peer windows -> bitonic sort -> same splitters everywhere
+        api.sort_splitters(keys, n_local, direction, spl)
+        # 2-4 fused: count + exchange of counts, partition pass that scatters into the peers' receive buffers
         api.partition_exchange_kv(keys, vals, n_local, spl, direction, b["keys"], b["vals"], cap,
                                   meta[:world * world], meta[world * world:])
         # 5. local stable sort of the receive buffer, received count read on the device: no host round trip
-        dk, dv = (torch.empty(cap, dtype=torch.int32, device=keys.device) for _ in range(2))
-        if "scratch" not in b:  # ping-pong scratch of the local sort lives with the receive buffers
-            b["scratch"] = [torch.empty(cap, dtype=torch.int32, device=keys.device) for _ in range(2)]
-        bk, bv = b["scratch"]
-        api.sort_kv_dyn(dk, dv, bk, bv, b["keys"][rank], b["vals"][rank], cap, meta[world * world:], direction)
+        api.sort_kv_dyn(w["dk"], w["dv"], w["bk"], w["bv"], b["keys"][rank], b["vals"][rank], cap,
+                        meta[world * world:], direction)
+        if not sync:
+            return w["dk"], w["dv"], meta, None
         host = meta.cpu()  # the only synchronisation: after everything is queued
+        check_p2p()
         if int(host[-1]) == 0:
-            return dk, dv, int(host[-2]), host[:world * world].reshape(world, world)
+            return w["dk"], w["dv"], int(host[-2]), host[:world * world].reshape(world, world)
         # some rank would receive more than `cap` pairs: nothing was sent, every rank takes the NCCL path below
+    if spl is None:
+        # 1. regular samples of the local keys, in ordered space
+        ns = min(samples_per_rank, max(n_local, 1))
+        step = max(n_local // ns, 1)
+        local = _u32_as_i64(keys[:n_local:step][:ns]) ^ flip
+        if local.numel() < ns:  # tiny shards: pad by repetition so every rank contributes ns samples
+            pad = local[-1:].expand(ns - local.numel()) if local.numel() else torch.zeros(ns, dtype=torch.int64,
+                                                                                        device=keys.device)
+            local = torch.cat([local, pad])
+        gathered = torch.empty(world * ns, dtype=torch.int64, device=keys.device)
+        dist.all_gather_into_tensor(gathered, local.contiguous(), group=group)
+        spl64 = choose_splitters(gathered, world)
+        spl = torch.where(spl64 >= 2**31, spl64 - 2**32, spl64).to(torch.int32).contiguous()
     # 2. local stable partition into `world` buckets
     pk, pv, counts = ops.partition(keys, vals, n_local, spl, world, direction)
     # 3. everyone learns everyone's bucket sizes

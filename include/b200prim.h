@@ -110,6 +110,13 @@ int b200_segmented_sort_kv_async(uint32_t *d_dstKey, uint32_t *d_dstVal, const u
                                  const uint32_t *d_srcVal, size_t batchSize, size_t arrayLength, uint32_t sortDir,
                                  b200_stream_t stream);
 
+/* Pre-size the library's per-device scratch for scans of up to n elements / sorts of up to N pairs (what initScan /
+ * initMergeSort do for the samples' own limits).  The *_async entry points grow their scratch on demand, and growing
+ * synchronises the device and is refused inside a stream capture (cudaErrorStreamCaptureUnsupported): reserve
+ * first when a call must stay asynchronous or is to be captured into a CUDA graph. */
+int b200_scan_reserve(size_t n);
+int b200_sort_reserve(size_t N);
+
 /* counter-based synthetic data, bit-identical to oracle_generate() (oracle/oracle.c): element i of
  * the stream depends only on (seed, first + i, kind, param), so shards are filled in place. */
 int b200_generate_async(void *d_out, size_t first, size_t n, uint64_t seed, int kind, uint32_t param,
@@ -166,6 +173,51 @@ int b200_partition_exchange_kv_async(const uint32_t *d_srcKey, const uint32_t *d
 /* histogram64 + histogram256 of the concatenation of all ranks' shards, on every rank, one kernel per rank */
 int b200_histogram_fused_allreduce_async(uint32_t *d_hist256, uint32_t *d_hist64, const void *d_data,
                                          size_t byteCount, b200_stream_t stream);
+
+/* measured NVLink roofline of the exchange phases: GB/s at which the current device writes `bytes` from d_src into
+ * d_dst (a peer-mapped buffer).  mode 0: 4-byte lane stores, 1: 16-byte lane stores, 2: cp.async.bulk from shared
+ * memory, 3: cudaMemcpyAsync (copy engine; p2pBandwidthLatencyTest.cu:113-146).  Best of reps. */
+int b200_p2p_probe_store(void *d_dst, const void *d_src, size_t bytes, int mode, int reps, double *best_gbs,
+                         b200_stream_t stream);
+/* how long a fused kernel waits for a peer's word before it gives up and counts an error (default 30 s) */
+int b200_p2p_set_timeout_ms(unsigned ms);
+/* splitters of the sharded sort chosen on the device (one exchange, no collective call, no host round trip):
+ * d_splitters receives world-1 ascending values in ordered key space, identical on every rank */
+int b200_sort_splitters_async(const uint32_t *d_srcKey, size_t N, uint32_t sortDir, uint32_t *d_splitters,
+                              b200_stream_t stream);
+
+/* ---- sharded primitives for ONE host process that drives all GPUs of the node (csrc/sharded.cu) ----------------
+ * The reference's multi-GPU idiom (Samples/0_Introduction/simpleMultiGPU/simpleMultiGPU.cu:132-133,157-200): a
+ * loop of cudaSetDevice + asynchronous launches, then a loop of synchronisations.  b200_ctx_create enables peer
+ * access between the listed devices and gives each one an exchange window and a stream; the entry points take HOST
+ * arrays with one device pointer / one length per device (index i = devices[i]) and return a status.  The exchange
+ * each primitive needs is done by the kernels themselves over NVLink; there is no NCCL and no IPC in this mode.
+ * A peer that never arrives is reported as cudaErrorLaunchTimeout by the blocking calls and by b200_ctx_synchronize.
+ * Not thread-safe: one host thread per context; the devices of a context must not run other exchange calls. */
+typedef struct b200_ctx b200_ctx;
+int b200_ctx_create(int ndev, const int *devices, b200_ctx **ctx);
+int b200_ctx_destroy(b200_ctx *ctx);
+int b200_ctx_num_devices(const b200_ctx *ctx);
+int b200_ctx_stream(b200_ctx *ctx, int i, b200_stream_t *stream); /* the stream device i's work is enqueued on */
+int b200_ctx_synchronize(b200_ctx *ctx);
+/* histogram64 + histogram256 of the concatenation of all shards; every device's d_hist256[i] (256 u32) and
+ * d_hist64[i] (64 u32) receive the GLOBAL bins.  Asynchronous: b200_ctx_synchronize before reading. */
+int b200_histogram_sharded(b200_ctx *ctx, uint32_t *const *d_hist256, uint32_t *const *d_hist64,
+                           const void *const *d_data, const size_t *byteCount);
+/* sum over all shards, blocking.  int wraps like reduceCPU<int>; float/double: shard sums added in device order in
+ * fp64 (deterministic), rounded once. */
+int b200_reduce_sharded_i32(b200_ctx *ctx, const int32_t *const *d_in, const size_t *n, int32_t *h_result);
+int b200_reduce_sharded_f32(b200_ctx *ctx, const float *const *d_in, const size_t *n, float *h_result);
+int b200_reduce_sharded_f64(b200_ctx *ctx, const double *const *d_in, const size_t *n, double *h_result);
+/* exclusive scan of ONE array split into contiguous shards (device i holds slice i, n[i] elements).  Asynchronous. */
+int b200_scan_exclusive_sharded(b200_ctx *ctx, uint32_t *const *d_dst, const uint32_t *const *d_src, const size_t *n);
+/* stable key-value sort of the concatenation of all shards; device i ends up with the i-th key range (h_nOut[i]
+ * pairs) in d_dstKey[i] / d_dstVal[i] (dstCapacity pairs each; 1.25 x the largest shard is ample for random keys).
+ * Blocking.  cudaErrorMemoryAllocation (2) when a device would receive more than dstCapacity pairs: nothing was
+ * moved and h_nOut holds the sizes that are needed. */
+int b200_sort_kv_sharded(b200_ctx *ctx, uint32_t *const *d_dstKey, uint32_t *const *d_dstVal, size_t dstCapacity,
+                         const uint32_t *const *d_srcKey, const uint32_t *const *d_srcVal, const size_t *n,
+                         uint32_t sortDir, size_t *h_nOut);
 
 /* host-buffer variants: H2D copies, kernels and D2H of the result are all inside the call
  * (chunked and double-buffered so the copy engine and the SMs overlap); they synchronise before

@@ -1,8 +1,9 @@
 #!/usr/bin/env python3
 """Per-tile timeline of one radix pass (debug build: python cuda_samples_b200/build.py --trace).
     B200PRIM_LIB=cuda_samples_b200/libb200prim_trace.so python profiles/sort_trace.py
-Slots (globaltimer ns, thread 0 of each tile): 0 ticket drawn, 1 keys in registers, 2 ranked, 3 counts published,
-4 look-back done (digit 0), 5 all digits resolved (barrier), 6 keys+values staged in shared memory."""
+Slots (globaltimer ns, thread 0 of each tile), r02 order of the pass (early counts): 0 ticket drawn, 1 keys in
+registers, 2 per-warp digit counts done, 3 tile counts published, 6 ranked + keys staged, 4 look-back done (digit 0),
+5 all digits resolved and values staged (barrier).  SORT_LB=1|4|8 sets the look-back rows per round trip."""
 import ctypes
 import os
 import sys
@@ -14,6 +15,8 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import cuda_samples_b200 as prim  # noqa: E402
 from cuda_samples_b200._lib import lib  # noqa: E402
 
+if os.environ.get("SORT_LB"):
+    lib.b200_tune_sort_lookback(int(os.environ["SORT_LB"]))
 N = 1 << 28
 TILE = int(os.environ.get("B200_SORT_TILE", "8192"))
 tiles = (N + TILE - 1) // TILE
@@ -40,14 +43,14 @@ def stat(name, x):
                                                                   np.percentile(x, 50) / 1e3, np.percentile(x, 90) / 1e3))
 
 
-print("pass span %.1f us for %d tiles" % ((t[:, 6].max() - t[:, 0].min()) / 1e3, tiles))
+print("pass span %.1f us for %d tiles" % ((t[:, 5].max() - t[:, 0].min()) / 1e3, tiles))
 stat("ticket -> keys in registers", t[:, 1] - t[:, 0])
-stat("ranking (16 items)", t[:, 2] - t[:, 1])
+stat("early digit counts (16 REDs)", t[:, 2] - t[:, 1])
 stat("barrier + warp order + publish", t[:, 3] - t[:, 2])
-stat("publish -> staged in smem", t[:, 6] - t[:, 3])
-stat("staged -> look-back done (digit 0)", t[:, 4] - t[:, 6])
-stat("wait for all digits (barrier)", t[:, 5] - t[:, 4])
-stat("TOTAL ticket -> all digits resolved", t[:, 5] - t[:, 0])
+stat("publish -> ranked, keys staged", t[:, 6] - t[:, 3])
+stat("ranked -> look-back done (digit 0)", t[:, 4] - t[:, 6])
+stat("values staged + wait for all digits", t[:, 5] - t[:, 4])
+stat("TOTAL ticket -> ready to store", t[:, 5] - t[:, 0])
 raw = trace.cpu().numpy().reshape(tiles, 8)[:, 7]
 polls, stalls = (raw & 0xFFFFFFFF)[mid], (raw >> 32)[mid]
 print("look-back of digit 0: polls per tile mean %.1f p50 %.0f p90 %.0f; of which found an unpublished row: mean %.1f"
