@@ -422,6 +422,33 @@ def primitives_table(torch, dist, prim, mg, rank, world, peak, barrier, p2p=Fals
         "collective": (("sample sort: all_gather of samples (NCCL) + partition pass storing into the peers' receive "
                         "buffers over NVLink (no all-to-all call)") if p2p else
                        "sample sort: all_gather + all_to_all") if world > 1 else None}
+    if world > 1 and p2p:
+        # ---- exchange phase alone, against the NVLink roofline (north_star: "NVLink roofline for the exchange phases")
+        def step_exchange():
+            mg.sort_exchange_only(sk, sv, n, 1)
+        tx = max_over_ranks(torch, dist, time_steps(torch, step_exchange, 5, 2, barrier) / 5, world)
+        meta = mg.sort_exchange_only(sk, sv, n, 1).cpu().numpy()
+        torch.cuda.synchronize()
+        m = meta[:world * world].reshape(world, world)
+        sent = int(m[rank].sum() - m[rank, rank])
+        st = torch.tensor([sent], dtype=torch.int64, device="cuda")
+        dist.all_reduce(st)
+        mean_sent = int(st.item()) / world
+        probe = mg.nvlink_probe(sk, 4 * n, n)
+        pt = torch.tensor([probe[k] for k in sorted(probe)], dtype=torch.float64, device="cuda")
+        dist.all_reduce(pt, op=dist.ReduceOp.MIN)  # the slowest rank's figure per mode
+        probe = {k: round(float(v), 1) for k, v in zip(sorted(probe), pt.tolist())}
+        gbs = 8 * mean_sent / tx / 1e9
+        table["mergeSort_kv_2^28"]["exchange"] = {
+            "phase": "splitters on the device + bucket counts and their exchange + partition pass storing the runs into "
+                     "the peers' receive buffers + node-wide barrier (everything of the sort that crosses NVLink)",
+            "bytes_out_per_gpu": int(8 * mean_sent), "seconds": tx, "GB/s_per_gpu": round(gbs, 1),
+            "frac_of_900_nominal": round(gbs / 900.0, 4),
+            "nvlink_probe_GBs_per_direction_per_gpu": probe,
+            "frac_of_measured_peer_copy": round(gbs / probe["cudaMemcpyAsync"], 4) if probe.get("cudaMemcpyAsync") else None,
+            "note": "the phase also reads the shard twice from HBM (count, partition) and ranks every pair: its time "
+                    "is not pure link time; the small exchanges of the other primitives are latency-bound "
+                    "(<= 2 KiB per rank, ~8 us per exchange, tests/multi_gpu_check.py)"}
     if world == 1:
         def step_sort_desc():
             prim.mergeSort(dk, dv, bk, bv, sk, sv, n, 0)

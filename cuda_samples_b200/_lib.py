@@ -87,6 +87,7 @@ SIGNATURES = {
     "b200_host_probe_h2d": (ci, [vp, sz, ci, ctypes.POINTER(ctypes.c_double)]),
     "b200_tune_host_path": (ci, [ci, sz]),
     "b200_tune_hist_cluster": (ci, [ci]),
+    "b200_tune_hist_launch": (ci, [ci, ci]),
     "b200_tune_scan_tma": (ci, [ci]),
     "b200_tune_scan_backoff": (ci, [ci]),
     "b200_tune_sort_lookback": (ci, [ci]),

@@ -30,8 +30,8 @@ namespace b200 {
 #ifndef B200_HIST_THREADS
 #define B200_HIST_THREADS 1024
 #endif
-constexpr int kHistThreads = B200_HIST_THREADS;          // 1024 x 1 CTA per SM (default) or 512 x 2
-constexpr int kHistCtasPerSm = 1024 / kHistThreads;
+constexpr int kHistThreadsBig = B200_HIST_THREADS;       // 1 CTA of 1024 threads per SM
+constexpr int kHistThreadsSmall = 512;                   // short inputs: two calls' CTAs fit on an SM together
 #ifndef B200_HIST_UNROLL
 #define B200_HIST_UNROLL 8
 #endif
@@ -72,11 +72,21 @@ template <int BINS, int SH> __device__ __forceinline__ void count_vec(unsigned *
     count_word<BINS, SH>(table, lane4, v.w);
 }
 
-template <int MODE>
-__global__ void __launch_bounds__(kHistThreads, kHistCtasPerSm)
+// Programmatic dependent launch (the sample's driver calls histogram256() 17 times back to back,
+// histogram/main.cpp:161-170): every launch carries cudaLaunchAttributeProgrammaticStreamSerialization, the kernel
+// releases its dependents at its very top (griddepcontrol.launch_dependents) and waits for its predecessor
+// (griddepcontrol.wait) only before it touches what consecutive calls share -- the {count,sum} accumulators and the
+// output bins.  Call k+1 therefore zeroes its table and streams its input while call k folds, merges and drains; with
+// the 512-thread geometry used for short inputs the two calls' CTAs are co-resident on every SM.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+template <int MODE, int kHistThreads>
+__global__ void __launch_bounds__(kHistThreads, 1024 / kHistThreads)
     histogram_kernel(const unsigned char *__restrict__ data, size_t n, unsigned *__restrict__ out256,
                      unsigned *__restrict__ out64, unsigned *__restrict__ scratch, P2PArgs p2p)
 {
+    pdl_launch_dependents();
     constexpr int BINS = (MODE == kHist64) ? 64 : 256;
     constexpr int SH   = (MODE == kHist64) ? 2 : 0;
     __shared__ unsigned table[BINS * 32];
@@ -172,6 +182,7 @@ __global__ void __launch_bounds__(kHistThreads, kHistCtasPerSm)
         __syncthreads();
     if (crank != 0)
         return;
+    pdl_wait(); // the previous call on the stream has completed: accumulators re-armed, its output written
 
     // ---- leader, single-GPU modes: ONE 64-bit atomic per bin carries the count and the number of clusters that
     // have contributed; the thread that completes a bin writes it out and re-arms the accumulator.  No fence, no
@@ -256,6 +267,41 @@ __global__ void __launch_bounds__(kHistThreads, kHistCtasPerSm)
 }
 
 static int g_hist_cluster = 0; // CTAs per cluster (1, 2, 4 or 8; 2 packs 148 SMs exactly); 0 = by input size
+static int g_hist_pdl     = 1; // programmatic dependent launch between consecutive calls on a stream
+static int g_hist_small   = 1; // inputs under 128 MiB: 0 = 1024-thread CTAs, 1 / 2 = that many 512-thread CTAs per SM
+                               // (with 1, the CTAs of two consecutive calls are co-resident on every SM)
+
+template <int MODE, int THREADS>
+static int launch_hist_t(DeviceCtx *c, unsigned *out256, unsigned *out64, const void *d_data, size_t n,
+                         cudaStream_t stream, const P2PArgs *p2p, int cluster)
+{
+    // persistent: one CTA per SM, but never more CTAs than there are 16 KiB slabs of input
+    size_t       want  = (n / 16 + THREADS - 1) / THREADS;
+    const size_t slots = (size_t)c->num_sms * (THREADS == kHistThreadsSmall ? g_hist_small : 1);
+    int          grid  = (int)(want < slots ? want : slots);
+    grid               = (grid / cluster) * cluster;
+    if (grid < cluster)
+        grid = cluster;
+
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim            = dim3(grid);
+    cfg.blockDim           = dim3(THREADS);
+    cfg.dynamicSmemBytes   = 0;
+    cfg.stream             = stream;
+    cudaLaunchAttribute at[2];
+    at[0].id               = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = cluster;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    at[1].id               = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs              = at;
+    cfg.numAttrs           = g_hist_pdl ? 2 : 1;
+    B200_TRY(cudaLaunchKernelEx(&cfg, histogram_kernel<MODE, THREADS>, (const unsigned char *)d_data, n, out256, out64,
+                                (unsigned *)c->hist.ptr, p2p ? *p2p : P2PArgs()));
+    count_launch();
+    return 0;
+}
 
 template <int MODE>
 static int launch_hist(unsigned *out256, unsigned *out64, const void *d_data, size_t n, cudaStream_t stream,
@@ -269,37 +315,18 @@ static int launch_hist(unsigned *out256, unsigned *out64, const void *d_data, si
     // short inputs skip the two cluster barriers of the DSMEM merge (64 MiB: 16.9 vs 18.2 us); from 128 MiB on the
     // merge is free and halves the global atomics
     const int cluster = g_hist_cluster ? g_hist_cluster : (n < (128u << 20) ? 1 : 2);
-    // persistent: one CTA per SM, but never more CTAs than there are 16 KiB slabs of input
-    size_t want = (n / 16 + kHistThreads - 1) / kHistThreads;
-    const size_t slots = (size_t)c->num_sms * kHistCtasPerSm;
-    int    grid = (int)(want < slots ? want : slots);
-    grid        = (grid / cluster) * cluster;
-    if (grid < cluster)
-        grid = cluster;
-
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim            = dim3(grid);
-    cfg.blockDim           = dim3(kHistThreads);
-    cfg.dynamicSmemBytes   = 0;
-    cfg.stream             = stream;
-    cudaLaunchAttribute at[1];
-    at[0].id               = cudaLaunchAttributeClusterDimension;
-    at[0].val.clusterDim.x = cluster;
-    at[0].val.clusterDim.y = 1;
-    at[0].val.clusterDim.z = 1;
-    cfg.attrs              = at;
-    cfg.numAttrs           = 1;
-    B200_TRY(cudaLaunchKernelEx(&cfg, histogram_kernel<MODE>, (const unsigned char *)d_data, n, out256, out64,
-                                (unsigned *)c->hist.ptr, p2p ? *p2p : P2PArgs()));
-    count_launch();
-    return 0;
+    if (g_hist_small && cluster == 1 && n < (128u << 20))
+        return launch_hist_t<MODE, kHistThreadsSmall>(c, out256, out64, d_data, n, stream, p2p, cluster);
+    return launch_hist_t<MODE, kHistThreadsBig>(c, out256, out64, d_data, n, stream, p2p, cluster);
 }
 
 int hist_preload()
 {
     cudaFuncAttributes fa;
-    B200_TRY(cudaFuncGetAttributes(&fa, histogram_kernel<kHistFusedP2P>));
-    B200_TRY(cudaFuncGetAttributes(&fa, histogram_kernel<kHistFused>));
+    B200_TRY(cudaFuncGetAttributes(&fa, histogram_kernel<kHistFusedP2P, kHistThreadsBig>));
+    B200_TRY(cudaFuncGetAttributes(&fa, histogram_kernel<kHistFusedP2P, kHistThreadsSmall>));
+    B200_TRY(cudaFuncGetAttributes(&fa, histogram_kernel<kHistFused, kHistThreadsBig>));
+    B200_TRY(cudaFuncGetAttributes(&fa, histogram_kernel<kHistFused, kHistThreadsSmall>));
     int        st = 0;
     DeviceCtx *c  = ctx(&st);
     if (!c)
@@ -335,6 +362,14 @@ extern "C" int b200_histogram_fused_async(uint32_t *d_hist256, uint32_t *d_hist6
 }
 // tuning knob used by bench.py / tests (not part of the stable ABI)
 extern "C" int b200_tune_hist_cluster(int cluster) { return set_hist_cluster(cluster); }
+// pdl: 1 = consecutive calls on a stream overlap through programmatic dependent launch (default), 0 = plain launches;
+// small_ctas: inputs under 128 MiB run with 0 = 1024-thread CTAs, 1 (default) / 2 = one / two 512-thread CTAs per SM
+extern "C" int b200_tune_hist_launch(int pdl, int small_ctas)
+{
+    g_hist_pdl   = pdl != 0;
+    g_hist_small = small_ctas < 0 ? 0 : (small_ctas > 2 ? 2 : small_ctas);
+    return 0;
+}
 // Both histograms of the concatenation of ALL ranks' shards, on every rank, in one kernel per rank: the last CTA
 // stores its 256 bins into every peer's window over NVLink and sums the G payloads (b200_p2p_connect first).
 extern "C" int b200_histogram_fused_allreduce_async(uint32_t *d_hist256, uint32_t *d_hist64, const void *d_data,

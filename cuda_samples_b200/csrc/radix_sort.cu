@@ -52,6 +52,16 @@ constexpr int      kRadix       = 256;
 #define B200_SORT_LB_FIRST 0 // 1: the look-back runs BEFORE the ranking loop (prefix published ~5 us earlier: shorter
                              //    chains for every successor, but this tile waits for it up front)
 #endif
+#ifndef B200_SORT_VALS_BEFORE_OWNERS
+#define B200_SORT_VALS_BEFORE_OWNERS 0 // 1: the value loads are issued before the digit owners' phase
+#endif
+#ifndef B200_SORT_LEADER_HIGH
+#define B200_SORT_LEADER_HIGH 0 // 1: the group's HIGHEST lane bumps the counter (bfind, no brev)
+#endif
+#ifndef B200_SORT_LB_STEPS
+#define B200_SORT_LB_STEPS 4 // look-back round trips issued from INSIDE the ranking loop (0: look-back after it)
+#endif
+constexpr int      kLbSteps   = B200_SORT_LB_STEPS;
 constexpr int      kValsEarly = B200_SORT_VALS_EARLY;
 static_assert(!B200_SORT_PACKED || kValsEarly == kSortItems, "packed staging needs every value before the ranking loop");
 constexpr unsigned kDescA = 1u << 30, kDescP = 2u << 30, kDescValue = (1u << 30) - 1;
@@ -497,16 +507,29 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
     SORT_TRACE(tile, 2);
     __syncthreads();
 
+    unsigned val[kSortItems];
+    auto     load_vals = [&](int lo, int hi) {
+        if (full) {
+#pragma unroll
+            for (int i = lo; i < hi; i++)
+                val[i] = __ldg(vin + base + wbase + i * 32);
+        }
+        else {
+#pragma unroll
+            for (int i = lo; i < hi; i++)
+                val[i] = (wbase + i * 32 < valid) ? __ldg(vin + base + wbase + i * 32) : 0u;
+        }
+    };
+#if B200_SORT_VALS_BEFORE_OWNERS
+    load_vals(0, kValsEarly);
+#endif
     // ---- 2. per digit: add the warps' counts, publish the tile aggregate, scan, running scatter positions --------
     {
         unsigned count = 0, tile_start = 0;
-        unsigned c[kSortWarps];
         if (tid < kRadix) {
 #pragma unroll
-            for (int w = 0; w < kSortWarps; w++) {
-                c[w] = S.wcnt[w][tid];
-                count += c[w];
-            }
+            for (int w = 0; w < kSortWarps; w++)
+                count += S.wcnt[w][tid];
             st_relaxed_u32(desc + (size_t)tile * kRadix + tid, (tile == 0 ? kDescP : kDescA) | count);
             unsigned inc = count;
 #pragma unroll
@@ -527,9 +550,10 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
                 tile_start += (w < (int)warp) ? S.wsum[w] : 0u;
             unsigned run = tile_start;
 #pragma unroll
-            for (int w = 0; w < kSortWarps; w++) {
-                S.wcnt[w][tid] = run;
-                run += c[w];
+            for (int w = 0; w < kSortWarps; w++) { // (re-read rather than 16 registers kept across the barrier)
+                const unsigned cw = S.wcnt[w][tid];
+                S.wcnt[w][tid]    = run;
+                run += cw;
             }
             S.cnt[tid]    = count; // parked: the ranking loop needs every register
             S.tstart[tid] = tile_start;
@@ -537,73 +561,67 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
     }
     __syncthreads();
 
-    // look back: thread d walks over the earlier tiles' counts of digit d, kLB rows per round trip; publishes the
-    // inclusive prefix and leaves gofs[d] = global index of the digit's first slot minus its tile-local start
-    auto look_back = [&]() {
+    // Look-back state of digit owner `tid`: it walks over the earlier tiles' counts of its digit, kLB rows per round
+    // trip.  The round trips are issued from INSIDE the ranking loop (every kSortItems / kLbSteps keys: the loads of one
+    // step are consumed by the next, ~1500 cycles later), so the walk costs the tile no time of its own and the
+    // inclusive prefix is published several microseconds earlier -- which shortens every successor's walk.
+    unsigned  lb_excl = 0, lb_d[kLB];
+    int       lb_back = (int)tile - 1; // next row to consume
+    unsigned  lb_state = (tid < kRadix && tile > 0) ? 0u : 2u; // 0: nothing in flight, 1: lb_d in flight, 2: done
+#ifdef B200_SCAN_TRACE
+    unsigned lb_polls = 0;
+#endif
+    auto lb_issue = [&]() {
+#pragma unroll
+        for (int j = 0; j < kLB; j++)
+            lb_d[j] = (lb_back - j >= 0) ? ld_relaxed_u32(desc + tid + (size_t)(lb_back - j) * kRadix) : kDescP;
+        lb_state = 1;
+#ifdef B200_SCAN_TRACE
+        lb_polls++;
+#endif
+    };
+    auto lb_consume = [&]() {
+        bool done = false;
+#pragma unroll
+        for (int j = 0; j < kLB; j++) {
+            if (done || (lb_d[j] >> 30) == 0)
+                break; // prefix found, or a row that is not published yet: poll again from there
+            lb_excl += lb_d[j] & kDescValue;
+            lb_back--;
+            done = (lb_d[j] & kDescP) != 0;
+        }
+        lb_state = 0;
+        if (done) {
+            st_relaxed_u32(desc + (size_t)tile * kRadix + tid, kDescP | (lb_excl + S.cnt[tid]));
+            lb_state = 2;
+        }
+    };
+    auto lb_step = [&]() { // warp-uniform for warps 0..7, a no-op for the others
+        if (lb_state == 1)
+            lb_consume();
+        if (lb_state == 0)
+            lb_issue();
+    };
+    auto look_back_finish = [&]() {
         if (tid < kRadix) {
-            unsigned       excl  = 0;
-            const unsigned count = S.cnt[tid];
-            if (tile > 0) {
-                const unsigned *dp     = desc + tid;
-                long long       t_back = (long long)tile - 1;
-                bool            done   = false;
+            while (lb_state != 2)
+                lb_step();
 #ifdef B200_SCAN_TRACE
-                unsigned polls = 0, stalls = 0;
+            if (g_sort_trace && threadIdx.x == 0)
+                g_sort_trace[(size_t)tile * 8 + 7] = lb_polls;
 #endif
-                while (!done) {
-#ifdef B200_SCAN_TRACE
-                    polls++;
-#endif
-                    unsigned d[kLB];
-#pragma unroll
-                    for (int j = 0; j < kLB; j++)
-                        d[j] = (t_back - j >= 0) ? ld_relaxed_u32(dp + (size_t)(t_back - j) * kRadix) : kDescP;
-                    long long t = t_back;
-#pragma unroll
-                    for (int j = 0; j < kLB; j++) {
-                        if (done)
-                            break;
-                        if ((d[j] >> 30) == 0) {
-#ifdef B200_SCAN_TRACE
-                            stalls++;
-#endif
-                            break; // not published yet: poll again from this tile
-                        }
-                        excl += d[j] & kDescValue;
-                        t--;
-                        done = (d[j] & kDescP) != 0;
-                    }
-                    t_back = t;
-                }
-#ifdef B200_SCAN_TRACE
-                if (g_sort_trace && threadIdx.x == 0)
-                    g_sort_trace[(size_t)tile * 8 + 7] = ((unsigned long long)stalls << 32) | polls;
-#endif
-                st_relaxed_u32(desc + (size_t)tile * kRadix + tid, kDescP | (excl + count));
-            }
-            S.gofs[tid] = __ldg(gbase + tid) + excl - S.tstart[tid];
+            S.gofs[tid] = __ldg(gbase + tid) + lb_excl - S.tstart[tid];
             SORT_TRACE(tile, 4);
         }
     };
 #if B200_SORT_LB_FIRST
-    look_back();
+    look_back_finish();
 #endif
 
     // ---- 3. values, then ranking: the pair goes straight to its tile-local slot ---------------------------------
-    unsigned val[kSortItems];
-    auto     load_vals = [&](int lo, int hi) {
-        if (full) {
-#pragma unroll
-            for (int i = lo; i < hi; i++)
-                val[i] = __ldg(vin + base + wbase + i * 32);
-        }
-        else {
-#pragma unroll
-            for (int i = lo; i < hi; i++)
-                val[i] = (wbase + i * 32 < valid) ? __ldg(vin + base + wbase + i * 32) : 0u;
-        }
-    };
+#if !B200_SORT_VALS_BEFORE_OWNERS
     load_vals(0, kValsEarly);
+#endif
 #if !B200_SORT_PACKED
     unsigned slot2[kSortItems / 2]; // two 16-bit slots per register
 #endif
@@ -616,10 +634,18 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
         const unsigned mask  = match_digit(d);
         const unsigned below = mask & lt;
         unsigned       pre   = 0;
+#if B200_SORT_LEADER_HIGH
+        if ((mask & ~lt & ~(1u << lane)) == 0) // no higher lane in the group
+            pre = atomicAdd(mycnt + d, (unsigned)__popc(mask));
+        pre = __shfl_sync(0xffffffffu, pre, 31 - __clz(mask));
+#else
         if (below == 0)
             pre = atomicAdd(mycnt + d, (unsigned)__popc(mask));
-        pre                 = __shfl_sync(0xffffffffu, pre, __ffs(mask) - 1);
+        pre = __shfl_sync(0xffffffffu, pre, __ffs(mask) - 1);
+#endif
         const unsigned slot = pre + __popc(below);
+        if (kLbSteps > 0 && (i + 1) % (kSortItems / (kLbSteps > 0 ? kLbSteps : 1)) == 0)
+            lb_step();
 #if B200_SORT_PACKED
         S.pair[slot] = make_uint2(kk, val[i]);
 #else
@@ -636,7 +662,7 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
 #endif
     // ---- 4. look-back ----------------------------------------------------------------------------------------
 #if !B200_SORT_LB_FIRST
-    look_back();
+    look_back_finish();
 #endif
 #if !B200_SORT_PACKED
 #pragma unroll

@@ -282,6 +282,39 @@ def choose_splitters(samples_ordered, world):
     return s[idx]
 
 
+def sort_exchange_only(keys, vals, n_local, direction=1, group=None, capacity_factor=1.25):
+    """The exchange phase of sort_sharded alone (p2p path): splitters, bucket counts + their exchange, and the
+    partition pass that stores the bucket runs into the peers' receive buffers, closed by the node-wide barrier.
+    For bench.py's NVLink-roofline row.  -> device tensor meta [world*world counts | pairs received | overflow]."""
+    rank, world = _world(group)
+    b = _recv_buffers(n_local, capacity_factor, rank, world, group)
+    if "work" not in b:
+        sort_sharded(keys, vals, n_local, direction, group=group, capacity_factor=capacity_factor)
+    w = b["work"]
+    api.sort_splitters(keys, n_local, direction, w["spl"])
+    api.partition_exchange_kv(keys, vals, n_local, w["spl"], direction, b["keys"], b["vals"], b["capacity"],
+                              w["meta"][:world * world], w["meta"][world * world:])
+    return w["meta"]
+
+
+def nvlink_probe(src, nbytes, n_local, group=None, capacity_factor=1.25):
+    """Measured NVLink roofline for the exchange: every rank writes nbytes from `src` into the receive buffer of rank
+    (rank+1) % world at the same time.  -> {mode name: GB/s per direction per GPU on this rank}."""
+    rank, world = _world(group)
+    b = _recv_buffers(n_local, capacity_factor, rank, world, group)
+    peer = b["keys"][(rank + 1) % world]
+    nbytes = min(nbytes, 4 * b["capacity"])
+    out = {}
+    for mode, name in ((3, "cudaMemcpyAsync"), (1, "16-byte lane stores"), (0, "4-byte lane stores"),
+                       (2, "cp.async.bulk from shared memory")):
+        torch.cuda.synchronize()
+        dist.barrier(group=group)
+        out[name] = api.p2p_probe_store(peer, src, nbytes, mode, 5)
+    torch.cuda.synchronize()
+    dist.barrier(group=group)
+    return out
+
+
 def check_p2p():
     """Raise if any fused exchange on this rank ever lost a peer (sticky device-side count, csrc/p2p.cuh): the results
     of that call are void.  Synchronises the device."""
