@@ -463,6 +463,27 @@ def primitives_table(torch, dist, prim, mg, rank, world, peak, barrier, p2p=Fals
         table["mergeSort_kv_2^28_keys_mod_65536"] = {
             "Gkeys/s": round(N_ELEMS / t3 / 1e9, 3), "ms_per_call": round(t3 * 1e3, 3), "n_gpus": 1,
             "dataset": "D3-like: key = counter-based random % 65536 (the sample's rand() % 65536 shape), ascending"}
+    if world == 1:
+        # --- batched short-array sorts (sortingNetworks API): arrays <= 4096 pairs are sorted
+        #     inside one CTA's shared memory: 16 B of traffic per pair.  Keys like the sample's (rand() % 65536).
+        del sk, sv
+        for batch, L in ((16384, 64), (256, 4096), (1 << 20, 64), (16384, 4096)):
+            m = batch * L
+            bsk = torch.empty(m, dtype=torch.int32, device="cuda")
+            prim.generate(bsk, "key_mod", 0, m, 5, 65536)
+            bsv = torch.arange(m, dtype=torch.int32, device="cuda")
+            bdk, bdv = torch.empty_like(bsk), torch.empty_like(bsv)
+
+            def step_bitonic():
+                prim.bitonicSort(bdk, bdv, bsk, bsv, batch, L, 1)
+            tb = time_steps(torch, step_bitonic, 20, 4) / 20
+            table["bitonicSort_%dx%d" % (batch, L)] = {
+                "Gpairs/s": round(m / tb / 1e9, 3), "us_per_call": round(tb * 1e6, 2), "n_gpus": 1,
+                "GB/s_at_16B_per_pair": round(16 * m / tb / 1e9, 1),
+                "frac_of_measured_peak": round(16 * m / tb / 1e9 / peak, 4),
+                "note": "SM-bound, not HBM-bound: two stable radix passes (16-bit keys) + one on the array index, "
+                        "~70 instructions per pair per pass; the sample's 2^20-pair shapes are one wave of CTAs"}
+            del bsk, bsv, bdk, bdv
     return table
 
 

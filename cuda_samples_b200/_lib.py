@@ -88,6 +88,8 @@ SIGNATURES = {
     "b200_tune_host_path": (ci, [ci, sz]),
     "b200_tune_hist_cluster": (ci, [ci]),
     "b200_tune_hist_launch": (ci, [ci, ci]),
+    "b200_tune_scan_total_reverse": (ci, [ci]),
+    "b200_tune_scan_pdl": (ci, [ci]),
     "b200_tune_scan_tma": (ci, [ci]),
     "b200_tune_scan_backoff": (ci, [ci]),
     "b200_tune_sort_lookback": (ci, [ci]),

@@ -158,6 +158,13 @@ __device__ __forceinline__ void st_release_u32(unsigned *p, unsigned v)
     asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
+// ---- programmatic dependent launch: a kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may
+// start once every CTA of its predecessor on the stream has executed launch_dependents (or exited); it must not
+// touch anything the predecessor produces before its own griddepcontrol.wait, which returns when the predecessor
+// has completed and its memory operations are visible.  Both are no-ops in a kernel launched the ordinary way.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ---- mbarrier + 1-D bulk async copy (TMA engine; SASS: UBLKCP) -------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t *bar, unsigned count)
 {

@@ -78,8 +78,6 @@ template <int BINS, int SH> __device__ __forceinline__ void count_vec(unsigned *
 // (griddepcontrol.wait) only before it touches what consecutive calls share -- the {count,sum} accumulators and the
 // output bins.  Call k+1 therefore zeroes its table and streams its input while call k folds, merges and drains; with
 // the 512-thread geometry used for short inputs the two calls' CTAs are co-resident on every SM.
-__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
-__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 template <int MODE, int kHistThreads>
 __global__ void __launch_bounds__(kHistThreads, 1024 / kHistThreads)

@@ -732,7 +732,13 @@ __global__ void __launch_bounds__(kSplitThreads, 1)
     __shared__ unsigned long long s_seq;
     const unsigned                step = n / kSplitSamples > 0 ? n / kSplitSamples : 1;
     for (unsigned i = threadIdx.x; i < kSplitSamples; i += kSplitThreads) {
-        const unsigned long long idx = (unsigned long long)i * step;
+        // stratified, jittered positions: regular positions alias with periodic key patterns (keys = f(i mod 4096)
+        // sampled every 2048 elements show two values) and would pick useless splitters
+        unsigned h = i * 2654435761u + 0x9E3779B9u;
+        h ^= h >> 15;
+        h *= 2246822519u;
+        h ^= h >> 13;
+        const unsigned long long idx = (unsigned long long)i * step + h % step;
         s_own[i] = n ? (keys[idx < n ? idx : n - 1] ^ flip) : 0xffffffffu; // an empty shard votes for "high"
     }
     __syncthreads();

@@ -138,13 +138,17 @@ __global__ void __launch_bounds__(kReduceThreads, kReduceCtasPerSm)
     reduce_kernel(const typename L::Elem *__restrict__ in, size_t n, typename L::Elem *__restrict__ out,
                   size_t out_len, unsigned *__restrict__ ticket, typename L::Part *__restrict__ partials,
                   double *__restrict__ out_f64, const typename L::Part *__restrict__ chain_in,
-                  typename L::Part *__restrict__ chain_out, ReduceExchange ex)
+                  typename L::Part *__restrict__ chain_out, ReduceExchange ex, bool reverse)
 {
     typedef typename L::Elem Elem;
     typedef typename L::Part Part;
     constexpr int kPerVec = 16 / sizeof(Elem);
     __shared__ Part s_part[32];
     __shared__ bool s_last;
+    // A kernel behind this one that opted in to programmatic dependent launch (the chained scan of a sharded scan,
+    // which needs this kernel's result -- the carry -- only when its first tile publishes) may start filling its
+    // pipeline while the last CTA here is still exchanging the shard totals with the peers.
+    pdl_launch_dependents();
 
     L acc;
     // split [0,n) into scalar head (to 16-byte alignment), vector body, scalar tail
@@ -158,19 +162,22 @@ __global__ void __launch_bounds__(kReduceThreads, kReduceCtasPerSm)
 
     const size_t stride = (size_t)gridDim.x * kReduceThreads;
     size_t       v      = (size_t)blockIdx.x * kReduceThreads + threadIdx.x;
+    // reverse: walk the array from its end to its start, so that its HEAD is what the L2 holds when the kernel ends
+    // (the shard total of a sharded scan: the scan that follows starts at the head and finds it cached)
+    auto at = [&](size_t idx) { return vin + (reverse ? nvec - 1 - idx : idx); };
     // main loop: kUnroll independent 16-byte loads in flight per thread
     for (; v + (kReduceUnroll - 1) * stride < nvec; v += kReduceUnroll * stride) {
         uint4 r[kReduceUnroll];
 #pragma unroll
         for (int k = 0; k < kReduceUnroll; k++)
-            r[k] = ld_stream_u4(vin + v + k * stride);
+            r[k] = ld_stream_u4(at(v + k * stride));
         acc.add_vecs(r);
     }
     if (v < nvec) { // last partial round: independent guarded loads (no one-at-a-time latency chain)
         uint4 r[kReduceUnroll - 1];
 #pragma unroll
         for (int k = 0; k < kReduceUnroll - 1; k++)
-            r[k] = (v + k * stride < nvec) ? ld_stream_u4(vin + v + k * stride) : make_uint4(0, 0, 0, 0);
+            r[k] = (v + k * stride < nvec) ? ld_stream_u4(at(v + k * stride)) : make_uint4(0, 0, 0, 0);
 #pragma unroll
         for (int k = 0; k < kReduceUnroll - 1; k++)
             acc.add_vec(r[k]); // zeros are exact no-ops for every T
@@ -244,7 +251,8 @@ __global__ void __launch_bounds__(kReduceThreads, kReduceCtasPerSm)
 template <typename L>
 static int launch_reduce(const typename L::Elem *d_in, size_t n, typename L::Elem *d_out, size_t out_len,
                          cudaStream_t stream, double *d_out_f64 = nullptr, const ReduceExchange *ex = nullptr,
-                         Scratch *scratch = nullptr, const void *chain_in = nullptr, void *chain_out = nullptr)
+                         Scratch *scratch = nullptr, const void *chain_in = nullptr, void *chain_out = nullptr,
+                         bool reverse = false)
 {
     int        st = 0;
     DeviceCtx *c  = ctx(&st);
@@ -275,11 +283,11 @@ static int launch_reduce(const typename L::Elem *d_in, size_t n, typename L::Ele
     if (ex)
         reduce_kernel<L, true><<<grid, kReduceThreads, 0, stream>>>(d_in, n, d_out, kernel_out_len, ticket, partials,
                                                                    d_out_f64, (const Part *)chain_in,
-                                                                   (Part *)chain_out, *ex);
+                                                                   (Part *)chain_out, *ex, reverse);
     else
         reduce_kernel<L, false><<<grid, kReduceThreads, 0, stream>>>(d_in, n, d_out, kernel_out_len, ticket, partials,
                                                                     d_out_f64, (const Part *)chain_in,
-                                                                    (Part *)chain_out, ReduceExchange());
+                                                                    (Part *)chain_out, ReduceExchange(), reverse);
     count_launch();
     B200_TRY(cudaGetLastError());
     if (alias_out) {
@@ -389,8 +397,27 @@ extern "C" int b200_reduce_partial_exchange_async(int kind, const void *d_in, si
 
 // Sharded long scan, step 1 fused with its exchange: shard total -> every peer -> *d_carry = wrapping sum of the
 // lower ranks' totals (the d_carry argument of b200_scan_exclusive_async).  d_work: >= 2 + world doubles.
+static bool g_scan_total_reverse = true;
+extern "C" int b200_tune_scan_total_reverse(int on)
+{
+    g_scan_total_reverse = on != 0;
+    return 0;
+}
 extern "C" int b200_scan_total_exchange_async(uint32_t *d_carry, const uint32_t *d_src, size_t n, double *d_work,
                                               b200_stream_t stream)
 {
-    return b200_reduce_partial_exchange_async(0, d_src, n, d_work, 0, 1, d_work + 2, d_work + 1, d_carry, stream);
+    const P2PArgs *a = p2p_args();
+    if (!a || a->world == 0)
+        return (int)cudaErrorInvalidValue;
+    ReduceExchange ex;
+    ex.p2p      = *a;
+    ex.slots    = d_work;
+    ex.gathered = d_work + 2;
+    ex.sums     = d_work + 1;
+    ex.carry    = d_carry;
+    ex.index    = 0;
+    ex.count    = 1;
+    // the shard is read back to front: its head is still in the L2 when the chained scan starts there
+    return launch_reduce<LaneI32>((const int *)d_src, n, nullptr, 0, (cudaStream_t)stream, d_work, &ex, nullptr, nullptr,
+                                  nullptr, g_scan_total_reverse);
 }

@@ -425,7 +425,17 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
         fence_mbar_init();
     }
     __syncthreads();
-    const unsigned            carry = p.carry ? __ldg(p.carry) : 0u;
+    // The carry (seed of element 0: the sum of the lower shards of a sharded scan) is produced by the kernel in front
+    // of this one.  With programmatic dependent launch this kernel is already loading tiles and publishing aggregates
+    // while that kernel still exchanges shard totals with its peers; the carry is fetched -- behind
+    // griddepcontrol.wait -- only where a first tile's prefix is formed.  Nothing is written to dst before that: every
+    // tile's prefix descends from a first tile's.
+    auto carry_now = [&]() -> unsigned {
+        if (!p.carry)
+            return 0u;
+        pdl_wait();
+        return ld_relaxed_u32(p.carry);
+    };
     unsigned long long *const cdesc = desc + p.num_tiles; // chunk-level descriptors follow the tile-level ones
 
     if (warp == kScanWarps) {
@@ -481,7 +491,9 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
             if (lane == 0)
                 SCAN_TRACE(tile, 2);
             const unsigned aggregate = S.agg[s];
-            unsigned       prefix    = carry;
+            unsigned       prefix    = 0;
+            if (tile == first_tile)
+                prefix = carry_now();
             if (tile != first_tile) { // (a first tile's inclusive prefix was published by the scan warps)
                 const unsigned want_a = (epoch << 2) | kStA, want_p = (epoch << 2) | kStP;
                 const unsigned t_in   = tile - first_tile, chunk_in = t_in >> 5;
@@ -520,7 +532,7 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
                         if (fp)
                             break;
                         if (last - 31 < firstc) { // walked past the array's first chunk (cannot happen: chunk 0
-                            sum2 += carry;        // always publishes a prefix) -- the seed is the carry
+                            sum2 += carry_now();  // always publishes a prefix) -- the seed is the carry
                             break;
                         }
                         last -= 32;
@@ -602,7 +614,7 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
                     __threadfence_block();
                     const unsigned agg        = *reinterpret_cast<volatile unsigned *>(&S.agg[s]);
                     const unsigned first_tile = (tile / p.tpa) * p.tpa;
-                    st_relaxed_u64(desc + tile, tile == first_tile ? make_desc(S.epoch[s], kStP, carry + agg)
+                    st_relaxed_u64(desc + tile, tile == first_tile ? make_desc(S.epoch[s], kStP, carry_now() + agg)
                                                                    : make_desc(S.epoch[s], kStA, agg));
                 }
                 mbar_arrive(&S.agg_ready[s]);
@@ -708,6 +720,28 @@ static int  g_scan_backoff_ns = 100;
 
 using namespace b200;
 
+static bool g_scan_pdl = true; // a scan with a carry overlaps the tail of the kernel that produces the carry
+
+template <typename K>
+static int launch_tma(K kernel, unsigned grid, size_t smem, cudaStream_t stream, bool pdl, uint32_t *d_dst,
+                      const uint32_t *d_src, ScanParams p, unsigned long long *st64, unsigned long long *desc)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim            = dim3(grid);
+    cfg.blockDim           = dim3(kTmaThreads);
+    cfg.dynamicSmemBytes   = smem;
+    cfg.stream             = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id                                         = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs                                        = at;
+    // measured (profiles/r02n_scan_shard_l2_pdl.log): the overlap pays for shards up to ~128 MiB (80.1 -> 76.5 us);
+    // behind a longer total pass the early tiles only compete with it for HBM (2^27 elements: 286 -> 304 us)
+    cfg.numAttrs = (pdl && g_scan_pdl && (size_t)p.num_tiles * 8192u <= (40u << 20)) ? 1 : 0;
+    B200_TRY(cudaLaunchKernelEx(&cfg, kernel, d_dst, d_src, p, st64, desc));
+    return 0;
+}
+
 static int scan_impl(uint32_t *d_dst, const uint32_t *d_src, size_t batch, size_t L, const uint32_t *d_carry,
                      bool inclusive, b200_stream_t stream_)
 {
@@ -779,11 +813,13 @@ static int scan_impl(uint32_t *d_dst, const uint32_t *d_src, size_t batch, size_
         auto *st64 = reinterpret_cast<unsigned long long *>(state);
         if (big) {
             B200_TRY((cudaError_t)opt_in_smem(c, kAttrScanTma0, scan_tma_kernel<5, 5, 3>, sizeof(ScanTmaSmem<5, 5>)));
-            scan_tma_kernel<5, 5, 3><<<grid, kTmaThreads, sizeof(ScanTmaSmem<5, 5>), stream>>>(d_dst, d_src, p, st64, desc);
+            B200_TRY((cudaError_t)launch_tma(scan_tma_kernel<5, 5, 3>, grid, sizeof(ScanTmaSmem<5, 5>), stream,
+                                             d_carry != nullptr, d_dst, d_src, p, st64, desc));
         }
         else {
             B200_TRY((cudaError_t)opt_in_smem(c, kAttrScanTma1, scan_tma_kernel<4, 6, 3>, sizeof(ScanTmaSmem<4, 6>)));
-            scan_tma_kernel<4, 6, 3><<<grid, kTmaThreads, sizeof(ScanTmaSmem<4, 6>), stream>>>(d_dst, d_src, p, st64, desc);
+            B200_TRY((cudaError_t)launch_tma(scan_tma_kernel<4, 6, 3>, grid, sizeof(ScanTmaSmem<4, 6>), stream,
+                                             d_carry != nullptr, d_dst, d_src, p, st64, desc));
         }
     }
     else if (large)
@@ -855,6 +891,11 @@ int compact_tma(int32_t *d_dst, int32_t *d_count, const int32_t *d_src, size_t n
     return 0;
 }
 
+extern "C" int b200_tune_scan_pdl(int on)
+{
+    g_scan_pdl = on != 0;
+    return 0;
+}
 // tuning knob for tests / bench (not part of the stable ABI): 0 = register-staged chained scan only
 extern "C" int b200_tune_scan_tma(int enable)
 {

@@ -9,10 +9,177 @@
 //      -- one b200_partition_kv_async pass when batchSize <= 256, a full sort otherwise
 //   3. gather keys and values through perm2.
 // Same kernels as mergeSort (sort_hist4_kernel, sort_pass_kernel); three tiny kernels around them.
+//
+// Arrays of up to 4096 pairs -- the lengths the sorting networks are made for (bitonicSort.cu:42-96 sorts an array of
+// up to SHARED_SIZE_LIMIT = 1024 in one CTA's shared memory) -- never leave the SM: seg_sort_kernel loads a tile of
+// whole arrays (up to 4096 pairs) into shared memory, sorts it there with stable 8-bit radix passes and writes it
+// once: 16 B of traffic per pair instead of the >= 150 B of the composition above.
+//   * passes: one per key byte that actually VARIES inside the tile (OR/AND of the tile's keys; the sample's
+//     keys are < 65536: two passes), then -- when the tile holds several arrays -- one pass on the array index,
+//     which puts every array back in its place (LSD order: key bytes first, array index last);
+//   * a pass is the tile-local part of sort_pass_kernel: per-warp digit counts (one shared RED per pair), the
+//     digit owners scan them into scatter positions, eight-ballot match ranking, the pair goes to its slot in
+//     place (every thread holds its pairs in registers across the barrier);
+//   * stable, any array length, both directions (descending = ascending on ~key).
 #include "common.cuh"
 #include "internal.h"
 
 namespace b200 {
+
+constexpr int      kSegThreads = 512;
+constexpr int      kSegWarps   = kSegThreads / 32;
+constexpr int      kSegItems   = 8;
+constexpr unsigned kSegTile    = kSegThreads * kSegItems; // 4096 pairs
+constexpr unsigned kSegMaxArrays = 255;                    // per tile: the array index is an 8-bit digit, 255 = padding
+
+struct SegSmem {
+    uint2         pair[kSegTile];
+    unsigned char seg[kSegTile];
+    unsigned      wcnt[kSegWarps][256];
+    unsigned      wsum[8];
+    unsigned      bits[2 * kSegWarps]; // OR / AND of the keys per warp
+};
+
+__device__ __forceinline__ unsigned seg_match_digit(unsigned d)
+{
+    unsigned mask = 0xffffffffu;
+#pragma unroll
+    for (int b = 0; b < 8; b++) {
+        const bool     p = (d >> b) & 1u;
+        const unsigned v = __ballot_sync(0xffffffffu, p);
+        mask &= p ? v : ~v;
+    }
+    return mask;
+}
+
+__global__ void __launch_bounds__(kSegThreads, 2)
+    seg_sort_kernel(unsigned *__restrict__ dstK, unsigned *__restrict__ dstV, const unsigned *__restrict__ srcK,
+                    const unsigned *__restrict__ srcV, size_t batch, unsigned L, unsigned apc /* arrays per CTA */,
+                    unsigned magic /* ceil(2^32 / L) */, unsigned flip)
+{
+    extern __shared__ __align__(16) unsigned char seg_raw[];
+    SegSmem       &S    = *reinterpret_cast<SegSmem *>(seg_raw);
+    const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const unsigned lt = lanemask_lt();
+    const size_t   a0 = (size_t)blockIdx.x * apc;
+    const unsigned na = (unsigned)(batch - a0 < apc ? batch - a0 : apc);
+    const unsigned nv = na * L; // valid pairs of this tile
+    const size_t   g0 = a0 * L;
+
+    // ---- load (coalesced), find the key bits that vary inside the tile ------------------------------------------
+    unsigned key[kSegItems], val[kSegItems], sid[kSegItems];
+    unsigned all_or = 0, all_and = 0xffffffffu;
+#pragma unroll
+    for (int i = 0; i < kSegItems; i++) {
+        const unsigned e = warp * (kSegItems * 32) + i * 32 + lane;
+        if (e < nv) {
+            key[i] = __ldg(srcK + g0 + e);
+            val[i] = __ldg(srcV + g0 + e);
+            sid[i] = __umulhi(e, magic); // e / L, exact for e, L <= 4096
+            all_or |= key[i] ^ flip;
+            all_and &= key[i] ^ flip;
+        }
+        else {
+            key[i] = ~flip; // ordered value 0xffffffff: behind every real key of its digit in every pass
+            val[i] = 0;
+            sid[i] = 255;
+        }
+    }
+    all_or  = __reduce_or_sync(0xffffffffu, all_or);
+    all_and = __reduce_and_sync(0xffffffffu, all_and);
+    if (lane == 0) {
+        S.bits[warp]             = all_or;
+        S.bits[kSegWarps + warp] = all_and;
+    }
+    __syncthreads();
+    all_or = 0, all_and = 0xffffffffu;
+#pragma unroll
+    for (int w = 0; w < kSegWarps; w++) {
+        all_or |= S.bits[w];
+        all_and &= S.bits[kSegWarps + w];
+    }
+    const unsigned varying = nv ? (all_or ^ all_and) : 0u;
+    unsigned      *mycnt   = S.wcnt[warp];
+
+    // ---- passes: key bytes that vary (least significant first), then the array index -----------------------------
+    for (int pass = 0; pass < 5; pass++) {
+        if (pass < 4 ? ((varying >> (8 * pass)) & 255u) == 0 : apc == 1)
+            continue; // (tile-uniform)
+        if (pass > 0 || true) {
+#pragma unroll
+            for (int k = 0; k < 8; k++)
+                mycnt[k * 32 + lane] = 0;
+            __syncwarp();
+        }
+        auto digit = [&](int i) { return pass < 4 ? (((key[i] ^ flip) >> (8 * pass)) & 255u) : sid[i]; };
+#pragma unroll
+        for (int i = 0; i < kSegItems; i++)
+            atomicAdd(mycnt + digit(i), 1u);
+        __syncthreads();
+        unsigned count = 0, start = 0;
+        if (tid < 256) {
+#pragma unroll
+            for (int w = 0; w < kSegWarps; w++)
+                count += S.wcnt[w][tid];
+            unsigned inc = count;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                unsigned t = __shfl_up_sync(0xffffffffu, inc, d);
+                if (lane >= d)
+                    inc += t;
+            }
+            if (lane == 31)
+                S.wsum[warp] = inc;
+            start = inc - count;
+        }
+        __syncthreads();
+        if (tid < 256) {
+#pragma unroll
+            for (int w = 0; w < 8; w++)
+                start += (w < (int)warp) ? S.wsum[w] : 0u;
+#pragma unroll
+            for (int w = 0; w < kSegWarps; w++) {
+                const unsigned cw = S.wcnt[w][tid];
+                S.wcnt[w][tid]    = start;
+                start += cw;
+            }
+        }
+        __syncthreads();
+        // rank in index order (warp, item, lane) and scatter in place: every pair of the tile sits in registers
+#pragma unroll
+        for (int i = 0; i < kSegItems; i++) {
+            const unsigned d     = digit(i);
+            const unsigned mask  = seg_match_digit(d);
+            const unsigned below = mask & lt;
+            unsigned       pre   = 0;
+            if (below == 0)
+                pre = atomicAdd(mycnt + d, (unsigned)__popc(mask));
+            pre                 = __shfl_sync(0xffffffffu, pre, __ffs(mask) - 1);
+            const unsigned slot = pre + __popc(below);
+            S.pair[slot]        = make_uint2(key[i], val[i]);
+            S.seg[slot]         = (unsigned char)sid[i];
+        }
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < kSegItems; i++) {
+            const unsigned e  = warp * (kSegItems * 32) + i * 32 + lane;
+            const uint2    pr = S.pair[e];
+            key[i]            = pr.x;
+            val[i]            = pr.y;
+            sid[i]            = S.seg[e];
+        }
+        __syncthreads(); // (the counter rows are re-zeroed and the slots rewritten by the next pass)
+    }
+    // ---- store: position e of the sorted tile is pair e of the tile's arrays -------------------------------------
+#pragma unroll
+    for (int i = 0; i < kSegItems; i++) {
+        const unsigned e = warp * (kSegItems * 32) + i * 32 + lane;
+        if (e < nv) {
+            dstK[g0 + e] = key[i];
+            dstV[g0 + e] = val[i];
+        }
+    }
+}
 
 __global__ void iota_kernel(unsigned *out, size_t n)
 {
@@ -58,6 +225,21 @@ extern "C" int b200_segmented_sort_kv_async(uint32_t *d_dstKey, uint32_t *d_dstV
     DeviceCtx *c  = ctx(&st);
     if (!c)
         return st;
+    if (arrayLength <= kSegTile) { // short arrays are sorted inside one CTA's shared memory: 16 B of traffic per pair
+        unsigned apc = (unsigned)(kSegTile / arrayLength);
+        apc          = apc > kSegMaxArrays ? kSegMaxArrays : apc;
+        const size_t tiles = (batchSize + apc - 1) / apc;
+        if (tiles < (1ull << 31)) {
+            B200_TRY((cudaError_t)opt_in_smem(c, kAttrSegSort, seg_sort_kernel, sizeof(SegSmem)));
+            const unsigned magic = (unsigned)(((1ull << 32) + arrayLength - 1) / arrayLength);
+            seg_sort_kernel<<<(unsigned)tiles, kSegThreads, sizeof(SegSmem), stream>>>(
+                d_dstKey, d_dstVal, d_srcKey, d_srcVal, batchSize, (unsigned)arrayLength, apc, magic,
+                sortDir ? 0u : 0xffffffffu);
+            count_launch();
+            B200_TRY(cudaGetLastError());
+            return 0;
+        }
+    }
     // scratch: idx | permK | perm | bufK | bufV | seg | perm2 | (splitters, counts)
     B200_TRY((cudaError_t)ensure(c->stage[1], (7 * N + 1024) * sizeof(unsigned), stream));
     unsigned *w = reinterpret_cast<unsigned *>(c->stage[1].ptr);

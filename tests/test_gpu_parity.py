@@ -745,6 +745,31 @@ def test_batched_sort_sorting_networks_api(prim, batch, L, direction):
     assert (np.sort(gv.reshape(batch, L), axis=1) == vals.reshape(batch, L)).all()
 
 
+@pytest.mark.parametrize("batch,L", [(3, 4096), (5, 3000), (1000, 1), (700, 3), (7, 4097), (300, 17), (1, 4096),
+                                     (255, 16), (256, 16), (9, 2048), (2, 2049)])
+@pytest.mark.parametrize("keys_kind", ["u16", "u32", "constant", "high_byte"])
+def test_batched_sort_in_shared_memory_shapes(prim, batch, L, keys_kind):
+    """Arrays of <= 4096 pairs are sorted inside one CTA's shared memory (seg_sort_kernel): ragged lengths (padding),
+    tiles with 1 .. 255 arrays, keys whose bytes do or do not vary (passes are skipped per tile), full 32-bit keys,
+    both directions; 4097 / 8192 take the composition path -- same contract either side of the threshold."""
+    rng = np.random.default_rng(batch * 131 + L)
+    n = batch * L
+    keys = {"u16": lambda: rng.integers(0, 65536, n, dtype=np.uint32),
+            "u32": lambda: rng.integers(0, 2**32, n, dtype=np.uint64).astype(np.uint32),
+            "constant": lambda: np.full(n, 0xDEADBEEF, np.uint32),
+            "high_byte": lambda: (rng.integers(0, 7, n, dtype=np.uint32) << 24) | 0x00ABCD12}[keys_kind]()
+    vals = np.arange(n, dtype=np.uint32)
+    sk, sv = dev(as_i32(keys)), dev(as_i32(vals))
+    for direction in (1, 0):
+        dk, dv = torch.full((n,), -1, dtype=torch.int32).cuda(), torch.full((n,), -1, dtype=torch.int32).cuda()
+        prim.bitonicSort(dk, dv, sk, sv, batch, L, direction)
+        gk, gv = dk.cpu().numpy().view(np.uint32), dv.cpu().numpy().view(np.uint32)
+        order = np.argsort(keys.reshape(batch, L).astype(np.int64) * (1 if direction else -1), axis=1, kind="stable")
+        wk = np.take_along_axis(keys.reshape(batch, L), order, axis=1).reshape(-1)
+        wv = np.take_along_axis(vals.reshape(batch, L), order, axis=1).reshape(-1)
+        assert (gk == wk).all() and (gv == wv).all(), (batch, L, keys_kind, direction)
+
+
 # ============================================================ peer-window exchange (world = 1) and dyn-count sort
 def test_sort_with_device_side_count(prim):
     """b200_sort_kv_dyn_async: the pair count is read on the device; capacity only sizes the launch."""
