@@ -508,7 +508,7 @@ def parity_block(torch, dist, prim, mg, oracle, rank, world, xi, xf, gpu_sums, e
         return t.cpu().numpy()
 
     def allgather_f64(value):
-        t = torch.tensor([value], dtype=torch.float64, device="cuda")
+        t = torch.tensor([float(np.asarray(value).reshape(-1)[0])], dtype=torch.float64, device="cuda")
         g = torch.empty(world, dtype=torch.float64, device="cuda")
         if world > 1:
             dist.all_gather_into_tensor(g, t)

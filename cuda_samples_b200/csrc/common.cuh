@@ -50,6 +50,7 @@ struct DeviceCtx {
     Scratch hist;         // accumulators + ticket
     Scratch scan;         // state + tile descriptors
     Scratch sort;         // digit histograms + descriptors
+    Scratch sort_pairs;   // two (key, value) pair buffers for the intermediate results of the radix passes
     Scratch image;        // integral image: band / block carries
     Scratch stage[2];     // device staging chunks of the host-buffer entry points
     Scratch host_work;    // their own reduce scratch + chunk rows (never shared with the *_async entry points)

@@ -132,7 +132,10 @@ extern "C" int b200_release_scratch_of(int which)
     switch (which) {
     case 0: release(c->hist); break;
     case 1: release(c->scan); break;
-    case 2: release(c->sort); break;
+    case 2:
+        release(c->sort);
+        release(c->sort_pairs);
+        break;
     case 3: release(c->reduce); break;
     default: return (int)cudaErrorInvalidValue;
     }
@@ -150,6 +153,7 @@ extern "C" int b200_release_scratch(void)
     release(c->hist);
     release(c->scan);
     release(c->sort);
+    release(c->sort_pairs);
     release(c->image);
     release(c->stage[0]);
     release(c->stage[1]);

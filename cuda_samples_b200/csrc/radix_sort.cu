@@ -432,7 +432,11 @@ __global__ void __launch_bounds__(kHist4Threads, 1)
 //   5. every digit's run leaves as contiguous stores.
 // Index order inside the tile = (warp, item, lane): ranks are stable by construction.
 // ---------------------------------------------------------------------------------------------------
-template <bool kBucket, int kLB, bool kPeer = false>
+// kIO: layout of the pass's input / output.  0: keys and values in separate arrays on both sides (the caller's
+// layout); 1: separate in, interleaved (key, value) pairs out; 2: pairs in, pairs out; 3: pairs in, separate out.
+// The three intermediate results of a four-pass sort live in library-owned pair buffers: one 8-byte load and one 8-byte
+// store per pair instead of two of each, and a digit run is one contiguous 8 B x count segment.
+template <bool kBucket, int kLB, bool kPeer = false, int kIO = 0>
 __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
     sort_pass_kernel(const unsigned *__restrict__ kin, const unsigned *__restrict__ vin, unsigned *__restrict__ kout,
                      unsigned *__restrict__ vout, unsigned n, unsigned shift, unsigned flip,
@@ -476,7 +480,20 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
     const unsigned wbase = warp * (kSortItems * 32) + lane;
     const unsigned pad   = ~flip; // (pad ^ flip) = 0xffffffff: last digit in every pass, ranks after all valid keys
     unsigned      *mycnt = S.wcnt[warp];
-    if (full) {
+    constexpr bool kInPk = (kIO == 2 || kIO == 3), kOutPk = (kIO == 1 || kIO == 2);
+    unsigned       val[kSortItems];
+    if (kInPk) { // one 8-byte load brings the pair
+        const uint2 *pin = reinterpret_cast<const uint2 *>(kin);
+#pragma unroll
+        for (int i = 0; i < kSortItems; i++) {
+            uint2 kv = make_uint2(pad, 0u);
+            if (full || wbase + i * 32 < valid)
+                kv = __ldg(pin + base + wbase + i * 32);
+            key[i] = kv.x;
+            val[i] = kv.y;
+        }
+    }
+    else if (full) {
 #pragma unroll
         for (int i = 0; i < kSortItems; i++)
             key[i] = __ldg(kin + base + wbase + i * 32);
@@ -507,8 +524,9 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
     SORT_TRACE(tile, 2);
     __syncthreads();
 
-    unsigned val[kSortItems];
     auto     load_vals = [&](int lo, int hi) {
+        if (kInPk)
+            return; // the values came with the keys
         if (full) {
 #pragma unroll
             for (int i = lo; i < hi; i++)
@@ -691,6 +709,17 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
             }
         }
     }
+    else if (kOutPk) {
+        uint2 *pout = reinterpret_cast<uint2 *>(kout);
+#pragma unroll
+        for (int k = 0; k < kSortItems; k++) {
+            const unsigned j = tid + k * kSortThreads;
+            SORT_PAIR_AT(j);
+            const unsigned g = S.gofs[op(x)] + j;
+            if (full || j < valid)
+                pout[g] = make_uint2(x, y);
+        }
+    }
     else if (full) {
 #pragma unroll
         for (int k = 0; k < kSortItems; k++) {
@@ -773,6 +802,8 @@ __global__ void __launch_bounds__(kSplitThreads, 1)
 constexpr size_t kSortOffHist = 16, kSortOffTickets = 16 + 4 * kRadix * 4, kSortOffDesc = kSortOffTickets + 16;
 
 static int g_sort_lb = 4; // look-back descriptors fetched per round trip (1, 4 or 8)
+static bool g_sort_pairs = true; // intermediate results as (key, value) pairs in library-owned buffers (2 x 8N bytes)
+constexpr size_t kSortPairsMin = 1u << 16;
 
 template <bool kBucket, int kLB>
 static int launch_pass(unsigned tiles, cudaStream_t stream, const unsigned *kin, const unsigned *vin, unsigned *kout,
@@ -789,6 +820,24 @@ static int launch_pass(unsigned tiles, cudaStream_t stream, const unsigned *kin,
     }
     sort_pass_kernel<kBucket, kLB><<<tiles, kSortThreads, sizeof(SortSmem), stream>>>(
         kin, vin, kout, vout, n, shift, flip, spl, nspl, gbase, ticket, desc, NoPeer(), n_dev);
+    return (int)cudaGetLastError();
+}
+
+// passes of the pair-buffer pipeline (kLB = 4 only): kIO 1 / 2 / 3
+template <int kIO>
+static int launch_pass_io(unsigned tiles, cudaStream_t stream, const void *in_a, const void *in_b, void *out_a,
+                          void *out_b, unsigned n, unsigned shift, unsigned flip, const unsigned *gbase,
+                          unsigned *ticket, unsigned *desc, const unsigned *n_dev)
+{
+    int        st = 0;
+    DeviceCtx *c  = ctx(&st);
+    if (!c)
+        return st;
+    B200_TRY((cudaError_t)opt_in_smem(c, kAttrMisc0 << (kIO - 1), sort_pass_kernel<false, 4, false, kIO>,
+                                      sizeof(SortSmem)));
+    sort_pass_kernel<false, 4, false, kIO><<<tiles, kSortThreads, sizeof(SortSmem), stream>>>(
+        (const unsigned *)in_a, (const unsigned *)in_b, (unsigned *)out_a, (unsigned *)out_b, n, shift, flip, nullptr, 0u,
+        gbase, ticket, desc, NoPeer(), n_dev);
     return (int)cudaGetLastError();
 }
 
@@ -840,6 +889,25 @@ static int sort_kv(uint32_t *d_dstKey, uint32_t *d_dstVal, uint32_t *d_bufKey, u
         B200_TRY(cudaGetLastError());
     }
 
+    if (g_sort_pairs && g_sort_lb == 4 && N >= kSortPairsMin) {
+        // src -> P0 -> P1 -> P0 -> dst with the three intermediate results as (key, value) pairs in library scratch
+        if (ensure(c->sort_pairs, 2 * N * sizeof(uint2), stream) == 0) {
+            uint2    *P0 = reinterpret_cast<uint2 *>(c->sort_pairs.ptr), *P1 = P0 + N;
+            auto      gb = [&](int p) { return (const unsigned *)(ghist + p * kRadix); };
+            auto      ds = [&](int p) { return reinterpret_cast<unsigned *>(base + kSortOffDesc + p * desc_bytes); };
+            B200_TRY((cudaError_t)launch_pass_io<1>(tiles, stream, d_srcKey, d_srcVal, P0, nullptr, (unsigned)N, 0u, flip,
+                                                    gb(0), tickets + 0, ds(0), d_n));
+            B200_TRY((cudaError_t)launch_pass_io<2>(tiles, stream, P0, nullptr, P1, nullptr, (unsigned)N, 8u, flip, gb(1),
+                                                    tickets + 1, ds(1), d_n));
+            B200_TRY((cudaError_t)launch_pass_io<2>(tiles, stream, P1, nullptr, P0, nullptr, (unsigned)N, 16u, flip,
+                                                    gb(2), tickets + 2, ds(2), d_n));
+            B200_TRY((cudaError_t)launch_pass_io<3>(tiles, stream, P0, nullptr, d_dstKey, d_dstVal, (unsigned)N, 24u,
+                                                    flip, gb(3), tickets + 3, ds(3), d_n));
+            count_launch(5);
+            return 0;
+        }
+        cudaGetLastError(); // no room for the pair buffers: the caller's buf arrays carry the intermediate results
+    }
     const uint32_t *kin = d_srcKey, *vin = d_srcVal;
     for (int p = 0; p < 4; p++) {
         uint32_t *kout = (p & 1) ? d_dstKey : d_bufKey;
@@ -985,6 +1053,11 @@ extern "C" int b200_partition_exchange_kv_async(const uint32_t *d_srcKey, const 
     return b200_p2p_barrier_async(stream_);
 }
 
+extern "C" int b200_tune_sort_pairs(int on)
+{
+    g_sort_pairs = on != 0;
+    return 0;
+}
 // tuning knob for experiments (not part of the stable ABI)
 extern "C" int b200_tune_sort_lookback(int per_round)
 {
@@ -1002,6 +1075,11 @@ extern "C" int b200_sort_reserve(size_t N)
         return st;
     const size_t tiles = (N + kSortTile - 1) / kSortTile;
     B200_TRY((cudaError_t)ensure(c->sort, kSortOffDesc + 4 * tiles * kRadix * 4, 0));
+    if (g_sort_pairs && N >= kSortPairsMin)
+        B200_TRY((cudaError_t)ensure(c->sort_pairs, 2 * N * sizeof(uint2), 0));
+    B200_TRY((cudaError_t)opt_in_smem(c, kAttrMisc0, sort_pass_kernel<false, 4, false, 1>, sizeof(SortSmem)));
+    B200_TRY((cudaError_t)opt_in_smem(c, kAttrMisc1, sort_pass_kernel<false, 4, false, 2>, sizeof(SortSmem)));
+    B200_TRY((cudaError_t)opt_in_smem(c, kAttrMisc2, sort_pass_kernel<false, 4, false, 3>, sizeof(SortSmem)));
     B200_TRY((cudaError_t)opt_in_smem(c, kAttrSortHist4, sort_hist4_kernel, 4 * kRadix * 32 * 4));
     B200_TRY((cudaError_t)opt_in_smem(c, kAttrSortPass1, sort_pass_kernel<false, 4>, sizeof(SortSmem)));
     return 0;

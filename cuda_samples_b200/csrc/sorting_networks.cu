@@ -225,6 +225,13 @@ extern "C" int b200_segmented_sort_kv_async(uint32_t *d_dstKey, uint32_t *d_dstV
     DeviceCtx *c  = ctx(&st);
     if (!c)
         return st;
+    if (arrayLength == 1) { // every array is already sorted (and ceil(2^32 / 1) does not fit the kernel's 32-bit divisor)
+        if (d_dstKey != d_srcKey)
+            B200_TRY(cudaMemcpyAsync(d_dstKey, d_srcKey, N * sizeof(uint32_t), cudaMemcpyDeviceToDevice, stream));
+        if (d_dstVal != d_srcVal)
+            B200_TRY(cudaMemcpyAsync(d_dstVal, d_srcVal, N * sizeof(uint32_t), cudaMemcpyDeviceToDevice, stream));
+        return 0;
+    }
     if (arrayLength <= kSegTile) { // short arrays are sorted inside one CTA's shared memory: 16 B of traffic per pair
         unsigned apc = (unsigned)(kSegTile / arrayLength);
         apc          = apc > kSegMaxArrays ? kSegMaxArrays : apc;

@@ -12,6 +12,8 @@ import cuda_samples_b200 as prim  # noqa: E402
 
 if os.environ.get("SORT_LB"):  # look-back rows fetched per round trip (1, 4 or 8)
     prim.lib.b200_tune_sort_lookback(int(os.environ["SORT_LB"]))
+if os.environ.get("SORT_PAIRS"):  # 0: intermediate results in the caller's buf arrays, 1: library pair buffers
+    prim.lib.b200_tune_sort_pairs(int(os.environ["SORT_PAIRS"]))
 tag = sys.argv[1] if len(sys.argv) > 1 else os.environ.get("B200PRIM_LIB", "default")
 ok = True
 for n in (() if os.environ.get("SORT_CHECK_SKIP_PARITY") else (1, 31, 4096, 4097, 12345, (1 << 20) + 77, 1 << 24)):
