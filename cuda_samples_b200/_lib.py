@@ -94,6 +94,7 @@ SIGNATURES = {
     "b200_tune_scan_backoff": (ci, [ci]),
     "b200_tune_sort_lookback": (ci, [ci]),
     "b200_tune_sort_pairs": (ci, [ci]),
+    "b200_tune_scan_reload": (ci, [ci]),
     # drop-in entry points (the samples' own signatures)
     "initHistogram64": (None, []), "closeHistogram64": (None, []), "histogram64": (None, [vp, vp, u32]),
     "initHistogram256": (None, []), "closeHistogram256": (None, []), "histogram256": (None, [vp, vp, u32]),

@@ -97,6 +97,23 @@ __device__ __forceinline__ uint4 ld_stream_u4(const void *p)
                  : "l"(p));
     return r;
 }
+// L2 eviction-priority descriptors for ld/st/cp.async.bulk ... .L2::cache_hint (the fixed encodings createpolicy yields
+// for fraction 1.0): evict_first = the line is dead once touched, evict_last = a later kernel reads it again
+constexpr uint64_t kL2EvictFirst = 0x12F0000000000000ull, kL2EvictLast = 0x14F0000000000000ull;
+__device__ __forceinline__ uint4 ld_stream_hint_u4(const void *p, uint64_t policy)
+{
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p), "l"(policy));
+    return r;
+}
+__device__ __forceinline__ void st_stream_hint_u4(void *p, uint4 v, uint64_t policy)
+{
+    asm volatile("st.global.L1::no_allocate.L2::cache_hint.v4.u32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(p), "r"(v.x), "r"(v.y),
+                 "r"(v.z), "r"(v.w), "l"(policy)
+                 : "memory");
+}
 // same without .nc: for kernels that may run in place (the loaded line is later written by this CTA)
 __device__ __forceinline__ uint4 ld_once_u4(const void *p)
 {
@@ -184,8 +201,16 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, unsigned bytes)
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
                  : "memory");
 }
+__device__ __forceinline__ bool mbar_test(uint64_t *bar, unsigned parity);
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, unsigned parity)
 {
+#if B200_MBAR_GUARD // first runs of a new pipeline: a wait that cannot complete gives up after ~2 s (wrong results, no hang)
+    const long long t0 = clock64();
+    while (!mbar_test(bar, parity))
+        if (clock64() - t0 > 4000000000ll)
+            return;
+    return;
+#endif
     asm volatile("{\n"
                  ".reg .pred p;\n"
                  "WAIT_%=:\n"
@@ -217,6 +242,14 @@ __device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gsrc, unsig
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
                      smem_u32(smem_dst)),
                  "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_g2s_hint(void *smem_dst, const void *gsrc, unsigned bytes, uint64_t *bar,
+                                              uint64_t policy)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], "
+                 "%4;" ::"r"(smem_u32(smem_dst)),
+                 "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
                  : "memory");
 }
 // global -> L2 only (no shared memory is reserved while the line is in flight)

@@ -337,8 +337,13 @@ constexpr int kHist4Threads = 1024;
 
 __global__ void __launch_bounds__(kHist4Threads, 1)
     sort_hist4_kernel(const unsigned *__restrict__ keys, size_t n, unsigned flip, unsigned *__restrict__ ghist,
-                      unsigned *__restrict__ ticket, const unsigned *__restrict__ n_dev)
+                      unsigned *__restrict__ ticket, const unsigned *__restrict__ n_dev, uint4 *__restrict__ zero,
+                      size_t zero_vecs)
 {
+    // the look-back descriptors of the four passes start at zero: stored from here (fire and forget, under the key
+    // reads) instead of by a memset in front of the kernel
+    for (size_t i = (size_t)blockIdx.x * kHist4Threads + threadIdx.x; i < zero_vecs; i += (size_t)gridDim.x * kHist4Threads)
+        zero[i] = make_uint4(0u, 0u, 0u, 0u);
     if (n_dev) // pair count produced on the device (receive buffer of the multi-GPU sort); n is its capacity
         n = *n_dev < n ? *n_dev : n;
     extern __shared__ __align__(16) unsigned tab[]; // [4][256][32]
@@ -800,6 +805,7 @@ __global__ void __launch_bounds__(kSplitThreads, 1)
 // scratch layout (bytes): [0,16) hist ticket | [16, 16+4 KiB) digit offsets [4][256]
 //                         | [4112, 4128) pass tickets | descriptors [passes][tiles][256] from 4128
 constexpr size_t kSortOffHist = 16, kSortOffTickets = 16 + 4 * kRadix * 4, kSortOffDesc = kSortOffTickets + 16;
+static_assert(kSortOffDesc % 16 == 0, "descriptor rows are zeroed with 16-byte stores");
 
 static int g_sort_lb = 4; // look-back descriptors fetched per round trip (1, 4 or 8)
 static bool g_sort_pairs = true; // intermediate results as (key, value) pairs in library-owned buffers (2 x 8N bytes)
@@ -872,7 +878,7 @@ static int sort_kv(uint32_t *d_dstKey, uint32_t *d_dstVal, uint32_t *d_bufKey, u
     const size_t   need       = kSortOffDesc + 4 * desc_bytes;
     B200_TRY((cudaError_t)ensure(c->sort, need, stream));
     char *base = reinterpret_cast<char *>(c->sort.ptr);
-    B200_TRY(cudaMemsetAsync(base, 0, need, stream));
+    B200_TRY(cudaMemsetAsync(base, 0, kSortOffDesc, stream)); // ticket, digit histograms, pass tickets (4 KiB)
     unsigned *hticket = reinterpret_cast<unsigned *>(base);
     unsigned *ghist   = reinterpret_cast<unsigned *>(base + kSortOffHist);
     unsigned *tickets = reinterpret_cast<unsigned *>(base + kSortOffTickets);
@@ -884,8 +890,8 @@ static int sort_kv(uint32_t *d_dstKey, uint32_t *d_dstVal, uint32_t *d_bufKey, u
         int    grid = (int)(want < (size_t)c->num_sms ? want : (size_t)c->num_sms);
         if (grid < 1)
             grid = 1;
-        sort_hist4_kernel<<<grid, kHist4Threads, 4 * kRadix * 32 * 4, stream>>>(d_srcKey, N, flip, ghist, hticket,
-                                                                                d_n);
+        sort_hist4_kernel<<<grid, kHist4Threads, 4 * kRadix * 32 * 4, stream>>>(
+            d_srcKey, N, flip, ghist, hticket, d_n, reinterpret_cast<uint4 *>(base + kSortOffDesc), 4 * desc_bytes / 16);
         B200_TRY(cudaGetLastError());
     }
 

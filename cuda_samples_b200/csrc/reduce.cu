@@ -17,6 +17,9 @@
 #include "internal.h"
 #include "p2p.cuh"
 
+#ifndef B200_REDUCE_KEEP_L2
+#define B200_REDUCE_KEEP_L2 0
+#endif
 namespace b200 {
 
 constexpr int kReduceThreads = 512;
@@ -165,6 +168,10 @@ __global__ void __launch_bounds__(kReduceThreads, kReduceCtasPerSm)
     // reverse: walk the array from its end to its start, so that its HEAD is what the L2 holds when the kernel ends
     // (the shard total of a sharded scan: the scan that follows starts at the head and finds it cached)
     auto at = [&](size_t idx) { return vin + (reverse ? nvec - 1 - idx : idx); };
+#if B200_REDUCE_KEEP_L2
+    const uint64_t pol = reverse ? kL2EvictLast : 0x1000000000000000ull; // (evict_normal)
+#define ld_stream_u4(p) ld_stream_hint_u4(p, pol)
+#endif
     // main loop: kUnroll independent 16-byte loads in flight per thread
     for (; v + (kReduceUnroll - 1) * stride < nvec; v += kReduceUnroll * stride) {
         uint4 r[kReduceUnroll];
@@ -182,6 +189,9 @@ __global__ void __launch_bounds__(kReduceThreads, kReduceCtasPerSm)
         for (int k = 0; k < kReduceUnroll - 1; k++)
             acc.add_vec(r[k]); // zeros are exact no-ops for every T
     }
+#if B200_REDUCE_KEEP_L2
+#undef ld_stream_u4
+#endif
     if (blockIdx.x == 0) {
         for (size_t i = threadIdx.x; i < head; i += kReduceThreads)
             acc.add_scalar(in[i]);

@@ -20,6 +20,12 @@
 #include "common.cuh"
 #include "internal.h"
 
+#ifndef B200_SCAN_LOAD_EVICT_FIRST
+#define B200_SCAN_LOAD_EVICT_FIRST 0
+#endif
+#ifndef B200_SCAN_STORE_EVICT_FIRST
+#define B200_SCAN_STORE_EVICT_FIRST 0
+#endif
 namespace b200 {
 
 constexpr int      kScanThreads = 512;
@@ -376,18 +382,24 @@ constexpr int      kTmaLookWarps = 2;
 constexpr int      kTmaThreads   = kScanThreads + 32 * (1 + kTmaLookWarps); // 16 scan + 1 producer + 2 look-back
 constexpr unsigned kTileEnd      = 0xffffffffu;
 
-template <int kTmaRows, int kTmaStages>
+// kRing: slots of per-tile bookkeeping.  kRing == kTmaStages: a tile owns its stage from landing to the scan (the tile
+// waits for its prefix in shared memory).  kRing > kTmaStages ("reload"): the stage is handed back as soon as phase A
+// has summed the tile; phase B reads the tile a second time with ordinary 16-byte loads -- an L2 hit, the first read
+// was a few microseconds ago -- so a stage is busy for the landing time only and the look-ahead is bounded by the
+// bookkeeping ring, not by shared memory.
+template <int kTmaRows, int kTmaStages, int kRing = kTmaStages>
 struct ScanTmaSmem {
     static constexpr unsigned kTmaTile = kScanThreads * kTmaRows * 4;
     unsigned buf[kTmaStages][kTmaTile];     // tiles in flight / being scanned
     uint64_t full[kTmaStages];              // producer  -> all     : tile landed (tx bytes) / END marker
-    uint64_t agg_ready[kTmaStages];         // scan warps -> look-back: the 16 warp totals are in
-    uint64_t prefix_ready[kTmaStages];      // look-back -> scan warps: exclusive tile prefix is in
-    uint64_t scanned[kTmaStages];           // scan warps -> producer : results are in the stage
-    unsigned tile[kTmaStages], count[kTmaStages], epoch[kTmaStages];
-    unsigned wtot[kTmaStages][kScanWarps];  // per-warp totals of the tile
-    unsigned agg[kTmaStages], agg_cnt[kTmaStages];
-    unsigned prefix[kTmaStages];
+    uint64_t scanned[kTmaStages];           // scan warps -> producer : the stage's tile has been read
+    uint64_t agg_ready[kRing];              // scan warps -> look-back: the 16 warp totals are in
+    uint64_t prefix_ready[kRing];           // look-back -> scan warps: exclusive tile prefix is in
+    uint64_t done[kRing];                   // scan warps -> producer : the slot's tile is finished (reload only)
+    unsigned tile[kRing], count[kRing], epoch[kRing];
+    unsigned wtot[kRing][kScanWarps];       // per-warp totals of the tile
+    unsigned agg[kRing], agg_cnt[kRing];
+    unsigned prefix[kRing];
     unsigned end_index;                     // CTA-local index of the END marker (look-back warps)
 };
 
@@ -398,15 +410,17 @@ __device__ __forceinline__ void mbar_arrive(uint64_t *bar)
 
 // kCompact: the same pipeline as a stable stream compaction (compact.cu): the scanned quantity is the flag
 // (int)x > 0, and instead of the prefixes the kept elements themselves are stored at their prefix positions.
-template <int kTmaRows, int kTmaStages, int kTmaAhead, bool kCompact = false>
+template <int kTmaRows, int kTmaStages, int kTmaAhead, bool kCompact = false, int kRing = kTmaStages>
 __global__ void __launch_bounds__(kTmaThreads, 1)
     scan_tma_kernel(unsigned *dst, const unsigned *src, const ScanParams p, unsigned long long *state,
                     unsigned long long *desc)
 {
     // the end marker is passed on through agg_ready of the stages of indices a, a+1: their previous phases must
     // have been consumed by then, which holds when the ring is at least two stages longer than the look-ahead
-    static_assert(kTmaStages >= kTmaAhead + 2, "stage ring too short for the phase-A look-ahead");
-    typedef ScanTmaSmem<kTmaRows, kTmaStages> Smem;
+    static_assert(kRing >= kTmaAhead + 2, "bookkeeping ring too short for the phase-A look-ahead");
+    constexpr bool kReload = kRing != kTmaStages;
+    static_assert(!kReload || !kCompact, "the compaction keeps its tiles in shared memory");
+    typedef ScanTmaSmem<kTmaRows, kTmaStages, kRing> Smem;
     constexpr unsigned kTmaTile = Smem::kTmaTile;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     Smem          &S    = *reinterpret_cast<Smem *>(smem_raw);
@@ -415,11 +429,14 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
     if (threadIdx.x == 0) {
         for (int s = 0; s < kTmaStages; s++) {
             mbar_init(&S.full[s], 1);
-            mbar_init(&S.agg_ready[s], kScanWarps);
-            mbar_init(&S.prefix_ready[s], 1);
             mbar_init(&S.scanned[s], kScanWarps);
-            S.agg[s]     = 0;
-            S.agg_cnt[s] = 0;
+        }
+        for (int m = 0; m < kRing; m++) {
+            mbar_init(&S.agg_ready[m], kScanWarps);
+            mbar_init(&S.prefix_ready[m], 1);
+            mbar_init(&S.done[m], kScanWarps);
+            S.agg[m]     = 0;
+            S.agg_cnt[m] = 0;
         }
         S.end_index = 0xffffffffu;
         fence_mbar_init();
@@ -449,17 +466,19 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
         // tile has been read.
         unsigned k = 0;
         while (true) {
-            const unsigned           s      = k % kTmaStages;
+            const unsigned           s = k % kTmaStages, m = k % kRing;
             const unsigned long long drawn  = atomicAdd(state, 1ull);
             const unsigned           ticket = (unsigned)drawn, epoch = (unsigned)(drawn >> 32);
             if (k >= (unsigned)kTmaStages) // the scan warps have pulled the stage's previous tile into registers
                 mbar_wait(&S.scanned[s], (k / kTmaStages - 1) & 1);
+            if (kReload && k >= (unsigned)kRing) // ... and the slot's previous tile has been scanned and stored
+                mbar_wait(&S.done[m], (k / kRing - 1) & 1);
             if (ticket >= p.num_tiles) {
                 if (ticket == p.num_tiles + gridDim.x - 1) // the very last draw of this launch
                     *reinterpret_cast<volatile unsigned long long *>(state) =
                         (unsigned long long)((epoch + 1u) & 0x3fffffffu) << 32;
                 S.end_index = k;
-                S.tile[s]   = kTileEnd;
+                S.tile[m]   = kTileEnd;
                 mbar_arrive(&S.full[s]);
                 // (the scan warps pass the end on to the look-back warps through agg_ready)
                 break;
@@ -468,12 +487,16 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
             const size_t   off    = (size_t)a * p.L + (size_t)t * kTmaTile;
             const size_t   remain = p.L - (size_t)t * kTmaTile;
             const unsigned count  = remain < kTmaTile ? (unsigned)remain : kTmaTile;
-            S.tile[s]  = ticket;
-            S.count[s] = count;
-            S.epoch[s] = epoch;
+            S.tile[m]  = ticket;
+            S.count[m] = count;
+            S.epoch[m] = epoch;
             SCAN_TRACE(ticket, 0);
             mbar_expect_tx(&S.full[s], count * 4u);
+#if B200_SCAN_LOAD_EVICT_FIRST
+            bulk_g2s_hint(S.buf[s], src + off, count * 4u, &S.full[s], kL2EvictFirst);
+#else
             bulk_g2s(S.buf[s], src + off, count * 4u, &S.full[s]);
+#endif
             k++;
         }
         return;
@@ -482,7 +505,7 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
     if (warp > kScanWarps) {
         // ================================ look-back warps ==============================================
         for (unsigned k = warp - kScanWarps - 1;; k += kTmaLookWarps) {
-            const unsigned s = k % kTmaStages, par = (k / kTmaStages) & 1;
+            const unsigned s = k % kRing, par = (k / kRing) & 1; // (bookkeeping slot)
             mbar_wait(&S.agg_ready[s], par); // all 16 warp totals are in -- or the scan warps reached the end
             if (k >= *reinterpret_cast<volatile unsigned *>(&S.end_index))
                 break;
@@ -561,9 +584,24 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
     // ==================================== scan warps (16) ==============================================
     unsigned a = 0, end_index = 0xffffffffu;
     for (unsigned b = 0;; b++) {
+        uint4 v[kTmaRows];
+        // reload: the second read of tile b is issued here (its phase A ran kTmaAhead tiles ago, the lines are in L2)
+        // and lands under phase A of tile b + kTmaAhead
+        auto reload_tile = [&]() {
+            const unsigned mb = b % kRing, tile_b = S.tile[mb], count = S.count[mb], ab = tile_b / p.tpa;
+            const unsigned *in = src + (size_t)ab * p.L + (size_t)(tile_b - ab * p.tpa) * kTmaTile;
+#pragma unroll
+            for (int r = 0; r < kTmaRows; r++) {
+                const unsigned e = warp * (kTmaRows * 128) + r * 128 + lane * 4;
+                v[r]             = e < count ? ld_once_u4(in + e) : make_uint4(0, 0, 0, 0);
+            }
+        };
+        const bool early = kReload && b < a;
+        if (early)
+            reload_tile();
         // ---- phase A: warp totals of tiles up to kTmaAhead ahead; the completing warp publishes -------
         while (end_index == 0xffffffffu && a <= b + kTmaAhead) {
-            const unsigned s = a % kTmaStages;
+            const unsigned s = a % kTmaStages, m = a % kRing;
 #if B200_SCAN_EAGER_B
             if (a > b) {
                 // look-ahead is opportunistic: if the prefix of tile b arrives before tile a has landed, scan tile b
@@ -580,7 +618,7 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
             }
 #endif
             mbar_wait(&S.full[s], (a / kTmaStages) & 1);
-            const unsigned tile = S.tile[s];
+            const unsigned tile = S.tile[m];
             if (tile == kTileEnd) {
                 end_index = a;
                 // tell the look-back warps: the owners of indices a .. a+kTmaLookWarps-1 wait on agg_ready of those
@@ -588,10 +626,10 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
                 // kTmaAhead tiles ahead of the prefixes the look-back warps have already delivered.)
                 if (lane == 0)
                     for (unsigned jj = 0; jj < (unsigned)kTmaLookWarps; jj++)
-                        mbar_arrive(&S.agg_ready[(a + jj) % kTmaStages]);
+                        mbar_arrive(&S.agg_ready[(a + jj) % kRing]);
                 break;
             }
-            const unsigned count = S.count[s];
+            const unsigned count = S.count[m];
             unsigned       sum   = 0;
 #pragma unroll
             for (int r = 0; r < kTmaRows; r++) {
@@ -606,37 +644,42 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
             }
             sum = __reduce_add_sync(0xffffffffu, sum);
             if (lane == 0) {
-                S.wtot[s][warp] = sum;
-                atomicAdd(&S.agg[s], sum);
+                if (kReload) // every lane's shared loads have been consumed by the reduction: the stage can be refilled
+                    mbar_arrive(&S.scanned[s]);
+                S.wtot[m][warp] = sum;
+                atomicAdd(&S.agg[m], sum);
                 __threadfence_block();
-                if (atomicAdd(&S.agg_cnt[s], 1u) == kScanWarps - 1) {
+                if (atomicAdd(&S.agg_cnt[m], 1u) == kScanWarps - 1) {
                     // all 16 warp totals are in: publish for the tiles behind us right away
                     __threadfence_block();
-                    const unsigned agg        = *reinterpret_cast<volatile unsigned *>(&S.agg[s]);
+                    const unsigned agg        = *reinterpret_cast<volatile unsigned *>(&S.agg[m]);
                     const unsigned first_tile = (tile / p.tpa) * p.tpa;
-                    st_relaxed_u64(desc + tile, tile == first_tile ? make_desc(S.epoch[s], kStP, carry_now() + agg)
-                                                                   : make_desc(S.epoch[s], kStA, agg));
+                    st_relaxed_u64(desc + tile, tile == first_tile ? make_desc(S.epoch[m], kStP, carry_now() + agg)
+                                                                   : make_desc(S.epoch[m], kStA, agg));
                 }
-                mbar_arrive(&S.agg_ready[s]);
+                mbar_arrive(&S.agg_ready[m]);
             }
             a++;
         }
         if (b == end_index)
             break;
-        // ---- phase B: scan tile b in place in shared memory --------------------------------------------
-        const unsigned s = b % kTmaStages;
-        mbar_wait(&S.prefix_ready[s], (b / kTmaStages) & 1);
-        const unsigned count = S.count[s];
+        // ---- phase B: scan tile b (from its stage, or from the registers the reload filled) ---------------------
+        const unsigned s = b % kTmaStages, m = b % kRing;
+        if (kReload && !early)
+            reload_tile();
+        mbar_wait(&S.prefix_ready[m], (b / kRing) & 1);
+        const unsigned count = S.count[m];
         if (threadIdx.x == 0)
-            SCAN_TRACE(S.tile[s], 5);
-        uint4          v[kTmaRows];
+            SCAN_TRACE(S.tile[m], 5);
         unsigned       ebase[kTmaRows], tot[kTmaRows], inc[kTmaRows];
 #pragma unroll
         for (int r = 0; r < kTmaRows; r++) {
             ebase[r] = warp * (kTmaRows * 128) + r * 128 + lane * 4;
-            v[r]     = *reinterpret_cast<const uint4 *>(&S.buf[s][ebase[r]]);
-            if (ebase[r] >= count)
-                v[r] = make_uint4(0, 0, 0, 0);
+            if (!kReload) {
+                v[r] = *reinterpret_cast<const uint4 *>(&S.buf[s][ebase[r]]);
+                if (ebase[r] >= count)
+                    v[r] = make_uint4(0, 0, 0, 0);
+            }
             if (kCompact)
                 tot[r] = ((int)v[r].x > 0) + ((int)v[r].y > 0) + ((int)v[r].z > 0) + ((int)v[r].w > 0);
             else
@@ -651,21 +694,21 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
                 if (lane >= d)
                     inc[r] += t;
             }
-        unsigned x = (lane < kScanWarps) ? S.wtot[s][lane] : 0u, xi = x;
+        unsigned x = (lane < kScanWarps) ? S.wtot[m][lane] : 0u, xi = x;
 #pragma unroll
         for (int d = 1; d < kScanWarps; d <<= 1) {
             unsigned t = __shfl_up_sync(0xffffffffu, xi, d);
             if (lane >= d)
                 xi += t;
         }
-        unsigned run = S.prefix[s] + __shfl_sync(0xffffffffu, xi - x, warp);
-        const unsigned tile_b = S.tile[s];
-        // everything this warp needs from the stage is in registers now: hand the stage back to the producer
+        unsigned run = S.prefix[m] + __shfl_sync(0xffffffffu, xi - x, warp);
+        const unsigned tile_b = S.tile[m];
+        // everything this warp needs from the stage / the slot is in registers now: hand it back to the producer
         __syncwarp();
         if (threadIdx.x == 0)
             SCAN_TRACE(tile_b, 6);
         if (lane == 0)
-            mbar_arrive(&S.scanned[s]);
+            mbar_arrive(kReload ? &S.done[m] : &S.scanned[s]);
         const unsigned ab = tile_b / p.tpa;
         unsigned      *out = dst + (size_t)ab * p.L + (size_t)(tile_b - ab * p.tpa) * kTmaTile;
 #pragma unroll
@@ -704,8 +747,13 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
             o.y += v[r].y & p.incl;
             o.z += v[r].z & p.incl;
             o.w += v[r].w & p.incl;
-            if (ebase[r] < count)
+            if (ebase[r] < count) {
+#if B200_SCAN_STORE_EVICT_FIRST
+                st_stream_hint_u4(out + ebase[r], o, kL2EvictFirst);
+#else
                 st_stream_u4(out + ebase[r], o);
+#endif
+            }
         }
         if (kCompact && tile_b == p.num_tiles - 1 && warp == kScanWarps - 1 && lane == 0)
             *p.count_out = (int)run; // prefix + everything kept in the last tile
@@ -720,6 +768,15 @@ static int  g_scan_backoff_ns = 100;
 
 using namespace b200;
 
+#ifndef B200_SCAN_RELOAD_AHEAD
+#define B200_SCAN_RELOAD_AHEAD 6
+#endif
+static bool g_scan_reload = false; // long arrays: stages hold a tile for its landing time only, phase B re-reads it from L2
+extern "C" int b200_tune_scan_reload(int on)
+{
+    g_scan_reload = on != 0;
+    return 0;
+}
 static bool g_scan_pdl = true; // a scan with a carry overlaps the tail of the kernel that produces the carry
 
 template <typename K>
@@ -811,7 +868,14 @@ static int scan_impl(uint32_t *d_dst, const uint32_t *d_src, size_t batch, size_
         if (grid > p.num_tiles)
             grid = p.num_tiles;
         auto *st64 = reinterpret_cast<unsigned long long *>(state);
-        if (big) {
+        if (big && g_scan_reload) {
+            typedef ScanTmaSmem<5, 5, 16> SmemR;
+            B200_TRY((cudaError_t)opt_in_smem(c, kAttrScanTma3, scan_tma_kernel<5, 5, B200_SCAN_RELOAD_AHEAD, false, 16>,
+                                              sizeof(SmemR)));
+            B200_TRY((cudaError_t)launch_tma(scan_tma_kernel<5, 5, B200_SCAN_RELOAD_AHEAD, false, 16>, grid, sizeof(SmemR),
+                                             stream, d_carry != nullptr, d_dst, d_src, p, st64, desc));
+        }
+        else if (big) {
             B200_TRY((cudaError_t)opt_in_smem(c, kAttrScanTma0, scan_tma_kernel<5, 5, 3>, sizeof(ScanTmaSmem<5, 5>)));
             B200_TRY((cudaError_t)launch_tma(scan_tma_kernel<5, 5, 3>, grid, sizeof(ScanTmaSmem<5, 5>), stream,
                                              d_carry != nullptr, d_dst, d_src, p, st64, desc));
@@ -936,6 +1000,8 @@ int scan_preload()
         return st;
     B200_TRY((cudaError_t)opt_in_smem(c, kAttrScanTma0, scan_tma_kernel<5, 5, 3>, sizeof(ScanTmaSmem<5, 5>)));
     B200_TRY((cudaError_t)opt_in_smem(c, kAttrScanTma1, scan_tma_kernel<4, 6, 3>, sizeof(ScanTmaSmem<4, 6>)));
+    B200_TRY((cudaError_t)opt_in_smem(c, kAttrScanTma3, scan_tma_kernel<5, 5, B200_SCAN_RELOAD_AHEAD, false, 16>,
+                                      sizeof(ScanTmaSmem<5, 5, 16>)));
     cudaFuncAttributes fa;
     B200_TRY(cudaFuncGetAttributes(&fa, scan_kernel<true>));
     B200_TRY(cudaFuncGetAttributes(&fa, scan_kernel<false>));

@@ -350,6 +350,9 @@ def sort_sharded(keys, vals, n_local, direction=1, ops=None, group=None, samples
             mk = lambda n: torch.empty(n, dtype=torch.int32, device=keys.device)  # noqa: E731
             b["work"] = {"spl": mk(max(world - 1, 1)), "meta": mk(world * world + 2), "dk": mk(cap), "dv": mk(cap),
                          "bk": mk(cap), "bv": mk(cap)}
+            api.sort_reserve(max(cap, n_local))  # library scratch too: no allocation between kernels that wait on peers
+            torch.cuda.synchronize()
+            dist.barrier(group=group)
         w = b["work"]
         spl, meta = w["spl"], w["meta"]
         # 1. splitters on the device: regular samples -> peer windows -> bitonic sort -> same splitters everywhere

@@ -13,7 +13,7 @@ import cuda_samples_b200 as prim  # noqa: E402
 which = sys.argv[1] if len(sys.argv) > 1 else "all"
 N = 1 << 28
 torch.cuda.set_device(0)
-REPS = 3
+REPS = int(os.environ.get("PROFILE_REPS", "3"))
 
 if which in ("all", "reduce"):
     xi = torch.empty(N, dtype=torch.int32, device="cuda")
@@ -71,4 +71,15 @@ if which in ("all", "sort"):
     for _ in range(2):
         prim.mergeSort(dk, dv, bk, bv, sk, sv, N, 1)
     torch.cuda.synchronize()
+
+if which in ("all", "seg"):
+    for batch, L in ((16384, 64), (16384, 4096)):
+        n = batch * L
+        sk = torch.empty(n, dtype=torch.int32, device="cuda")
+        prim.generate(sk, "key_mod", 0, n, 2009, 65536)
+        sv = torch.arange(n, dtype=torch.int32, device="cuda")
+        dk, dv = torch.empty(n, dtype=torch.int32, device="cuda"), torch.empty(n, dtype=torch.int32, device="cuda")
+        for _ in range(2):
+            prim.bitonicSort(dk, dv, sk, sv, batch, L, 1)
+        torch.cuda.synchronize()
 print("done", which)

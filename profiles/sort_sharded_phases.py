@@ -31,18 +31,14 @@ for _ in range(REPS):
     dist.barrier()
     torch.cuda.synchronize()
     ev[0].record()
-    ns = 1024
-    step = max(n // ns, 1)
-    loc = (sk[:n:step][:ns].to(torch.int64) & 0xFFFFFFFF)
-    gathered = torch.empty(world * ns, dtype=torch.int64, device="cuda")
-    dist.all_gather_into_tensor(gathered, loc.contiguous())
-    spl64 = mg.choose_splitters(gathered, world)
-    spl = torch.where(spl64 >= 2**31, spl64 - 2**32, spl64).to(torch.int32).contiguous()
+    spl = b["work"]["spl"]
+    api.sort_splitters(sk, n, 1, spl)  # jittered samples -> peer windows -> bitonic sort -> the same splitters everywhere
     ev[1].record()
     meta = torch.empty(world * world + 2, dtype=torch.int32, device="cuda")
     api.partition_exchange_kv(sk, sv, n, spl, 1, b["keys"], b["vals"], cap, meta[:world * world], meta[world * world:])
     ev[2].record()
-    dk, dv, bk, bv = (torch.empty(cap, dtype=torch.int32, device="cuda") for _ in range(4))
+    w = b["work"]
+    dk, dv, bk, bv = w["dk"], w["dv"], w["bk"], w["bv"]
     ev[3].record()
     api.sort_kv_dyn(dk, dv, bk, bv, b["keys"][rank], b["vals"][rank], cap, meta[world * world:], 1)
     ev[4].record()
@@ -52,7 +48,7 @@ for _ in range(REPS):
     for i in range(5):
         acc[i] += ev[i].elapsed_time(ev[i + 1]) / REPS
 if rank == 0:
-    for name, t in zip(("splitters (torch + NCCL all_gather)", "partition + exchange (2 kernels)", "torch.empty x4",
+    for name, t in zip(("splitters (one kernel, peer windows)", "partition + exchange (2 kernels)", "(nothing)",
                         "local sort (dyn count)", "meta.cpu()"), acc):
         print("world=%d  %-38s %8.1f us" % (world, name, t * 1e3))
     print("world=%d  total %.1f us; received %d of capacity %d" % (world, sum(acc) * 1e3, int(host[-2]), cap))
