@@ -740,13 +740,11 @@ def run_ours(args):
     # PCIe roofline of the same run: every rank copies its 1 GiB pinned buffer 4 times back to back, all ranks between
     # the same two barriers; bytes of all ranks / the slowest rank's time = what this host feeds N GPUs AT ONCE
     # (per-rank bests summed would count moments when the other ranks had already finished)
-    prim.host_probe_h2d(hi, 4 * N_ELEMS, 1)
+    pcie_best = prim.host_probe_h2d(hi, 4 * N_ELEMS, 3)
     if barrier:
         barrier()
-    t0 = time.perf_counter()
-    pcie_best = prim.host_probe_h2d(hi, 4 * N_ELEMS, 4)
-    pcie_s = max_over_ranks(torch, dist, time.perf_counter() - t0, world)
-    pcie_gbs = 5 * 4 * N_ELEMS * world / pcie_s / 1e9  # the probe's warm-up copy is inside the interval too
+    pcie_s = max_over_ranks(torch, dist, prim.host_probe_h2d_sustained(xi, hi, 4 * N_ELEMS, 4), world)
+    pcie_gbs = 4 * 4 * N_ELEMS * world / pcie_s / 1e9
     pcie_t = torch.tensor([pcie_best], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(pcie_t)
@@ -821,7 +819,7 @@ def run_ours(args):
                     "api": "b200_reduce_i32_host + b200_reduce_f32_host per rank (pinned host input from "
                            "b200_host_alloc, H2D chunks overlapped with the kernels, result word read back)",
                     "pcie_gbs": pcie_gbs, "frac_of_pcie": e2e_value / pcie_gbs if pcie_gbs else None,
-                    "pcie_probe": "plain pinned cudaMemcpyAsync H2D of the same 1 GiB buffer, 5 copies back to back on "
+                    "pcie_probe": "plain pinned cudaMemcpyAsync H2D of the same 1 GiB buffer, 4 copies back to back on "
                                   "all %d rank(s) between two barriers: total bytes / slowest rank's time" % world,
                     "pcie_gbs_sum_of_per_rank_bests": pcie_sum_of_bests,
                     "host_buffer": host_info},

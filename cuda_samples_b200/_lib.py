@@ -85,6 +85,7 @@ SIGNATURES = {
     "b200_host_free": (ci, [vp]),
     "b200_host_alloc_info": (ci, [vp] + [ctypes.POINTER(ci)] * 4),
     "b200_host_probe_h2d": (ci, [vp, sz, ci, ctypes.POINTER(ctypes.c_double)]),
+    "b200_host_probe_h2d_sustained": (ci, [vp, vp, sz, ci, ctypes.POINTER(ctypes.c_double)]),
     "b200_tune_host_path": (ci, [ci, sz]),
     "b200_tune_hist_cluster": (ci, [ci]),
     "b200_tune_hist_launch": (ci, [ci, ci]),
@@ -94,6 +95,7 @@ SIGNATURES = {
     "b200_tune_scan_backoff": (ci, [ci]),
     "b200_tune_sort_lookback": (ci, [ci]),
     "b200_tune_sort_pairs": (ci, [ci]),
+    "b200_tune_sort_peer_bulk": (ci, [ci]),
     "b200_tune_scan_reload": (ci, [ci]),
     # drop-in entry points (the samples' own signatures)
     "initHistogram64": (None, []), "closeHistogram64": (None, []), "histogram64": (None, [vp, vp, u32]),

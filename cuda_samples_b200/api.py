@@ -249,7 +249,7 @@ def partition_exchange_kv(srcKey, srcVal, N, d_splitters, sortDir, recv_keys, re
     buffers (recv_keys / recv_vals: lists of `world` int device pointers).  See include/b200prim.h."""
     w = len(recv_keys)
     ka = (ctypes.c_void_p * w)(*recv_keys)
-    va = (ctypes.c_void_p * w)(*recv_vals)
+    va = (ctypes.c_void_p * w)(*recv_vals) if recv_vals is not None else None  # None: recv_keys are pair buffers
     check(lib.b200_partition_exchange_kv_async(_dptr(srcKey), _dptr(srcVal), N, _dptr(d_splitters), sortDir, ka, va,
                                                capacity, _dptr(d_matrix), _dptr(d_info), _stream(stream)),
           "partition_exchange_kv")
@@ -398,6 +398,14 @@ def host_probe_h2d(h_src, nbytes, reps=5):
     g = ctypes.c_double(0.0)
     check(lib.b200_host_probe_h2d(_hptr(h_src), nbytes, reps, ctypes.byref(g)), "b200_host_probe_h2d")
     return float(g.value)
+
+
+def host_probe_h2d_sustained(d_dst, h_src, nbytes, reps=4):
+    """reps back-to-back pinned H2D copies of nbytes into the device tensor d_dst -> seconds (first issue to last done)."""
+    t = ctypes.c_double(0.0)
+    check(lib.b200_host_probe_h2d_sustained(d_dst.data_ptr(), _hptr(h_src), nbytes, reps, ctypes.byref(t)),
+          "b200_host_probe_h2d_sustained")
+    return float(t.value)
 
 
 def tune_host_path(mode, chunk_bytes=0):

@@ -108,6 +108,15 @@ __device__ __forceinline__ uint4 ld_stream_hint_u4(const void *p, uint64_t polic
                  : "l"(p), "l"(policy));
     return r;
 }
+__device__ __forceinline__ uint4 ld_once_hint_u4(const void *p, uint64_t policy)
+{
+    uint4 r;
+    asm volatile("ld.global.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p), "l"(policy)
+                 : "memory");
+    return r;
+}
 __device__ __forceinline__ void st_stream_hint_u4(void *p, uint4 v, uint64_t policy)
 {
     asm volatile("st.global.L1::no_allocate.L2::cache_hint.v4.u32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(p), "r"(v.x), "r"(v.y),

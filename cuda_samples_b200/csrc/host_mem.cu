@@ -12,6 +12,7 @@
 //      pages from a thread pinned to that node's CPUs (if the process is allowed to run there),
 //   3. touches every page and registers the range with cudaHostRegister (mapped + portable).
 // b200_host_alloc_info reports where the pages actually are (move_pages query), so bench.py can print it.
+#include <chrono>
 #include "common.cuh"
 #include "internal.h"
 
@@ -333,5 +334,27 @@ extern "C" int b200_host_probe_h2d(const void *h_src, size_t bytes, int reps, do
     cudaStreamDestroy(s);
     cudaFree(d);
     *best_gbs = best;
+    return (int)e;
+}
+
+// reps back-to-back pinned H2D copies into a caller-provided device buffer; *seconds = host time from the first
+// cudaMemcpyAsync to the completion of the last (no allocation, stream or event creation inside the interval).  Ranks
+// that call this between the same two barriers measure what the host feeds all their GPUs AT ONCE.
+extern "C" int b200_host_probe_h2d_sustained(void *d_dst, const void *h_src, size_t bytes, int reps, double *seconds)
+{
+    if (!d_dst || !h_src || !bytes || reps < 1 || !seconds)
+        return (int)cudaErrorInvalidValue;
+    cudaStream_t s;
+    B200_TRY(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    cudaError_t e = cudaMemcpyAsync(d_dst, h_src, bytes < (1u << 20) ? bytes : (1u << 20), cudaMemcpyHostToDevice, s);
+    if (e == cudaSuccess)
+        e = cudaStreamSynchronize(s); // warm the path
+    const auto t0 = std::chrono::steady_clock::now();
+    for (int i = 0; i < reps && e == cudaSuccess; i++)
+        e = cudaMemcpyAsync(d_dst, h_src, bytes, cudaMemcpyHostToDevice, s);
+    if (e == cudaSuccess)
+        e = cudaStreamSynchronize(s);
+    *seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    cudaStreamDestroy(s);
     return (int)e;
 }

@@ -84,7 +84,7 @@ __device__ __forceinline__ unsigned long long sort_now()
 // shared memory of the pass kernel (dynamic)
 struct SortSmem {
 #if B200_SORT_PACKED
-    uint2    pair[kSortTile];             // (key, value) in digit order
+    uint2    pair[kSortTile + kP2PMaxRanks]; // (key, value) in digit order (+ room to re-space the runs of a peer pass)
 #else
     unsigned buf[kSortTile];              // keys in digit order
     unsigned vbuf[kSortTile];             // values in digit order
@@ -94,6 +94,7 @@ struct SortSmem {
     unsigned cnt[kRadix];                 // parking space (tile count / tile-local start per digit) while the
     unsigned tstart[kRadix];              //   ranking loop needs every register
     unsigned wsum[kRadix / 32];
+    unsigned respace[kP2PMaxRanks];       // peer pass: slots inserted in front of a bucket's run (parity match for bulk copies)
     unsigned splitters[kRadix];
     unsigned tile;
 };
@@ -101,8 +102,10 @@ struct SortSmem {
 // Peer variant of the partition (multi-GPU sample sort): bucket b IS rank b, and its run is stored straight into
 // rank b's receive buffer over NVLink instead of into a local array that an all-to-all would copy again.
 struct SortPeer {
-    unsigned long long k[kP2PMaxRanks], v[kP2PMaxRanks]; // receive buffers of every rank (peer-mapped)
+    unsigned long long k[kP2PMaxRanks], v[kP2PMaxRanks]; // receive buffers of every rank (peer-mapped); v[0] == 0:
+                                                         // k[r] holds (key, value) PAIRS (one 8-byte peer store per pair)
     const unsigned    *info;   // [0] n_out, [1] != 0: a receive buffer would overflow -> nothing is sent
+    unsigned           bulk;   // pair format only: runs leave through the bulk-copy engine instead of lane stores
 };
 struct NoPeer {};
 template <bool kPeer> struct PeerParam { typedef NoPeer type; };
@@ -338,7 +341,7 @@ constexpr int kHist4Threads = 1024;
 __global__ void __launch_bounds__(kHist4Threads, 1)
     sort_hist4_kernel(const unsigned *__restrict__ keys, size_t n, unsigned flip, unsigned *__restrict__ ghist,
                       unsigned *__restrict__ ticket, const unsigned *__restrict__ n_dev, uint4 *__restrict__ zero,
-                      size_t zero_vecs)
+                      size_t zero_vecs, bool pairs /* keys[2 i] is key i: the input is a (key, value) pair buffer */)
 {
     // the look-back descriptors of the four passes start at zero: stored from here (fire and forget, under the key
     // reads) instead of by a memset in front of the kernel
@@ -361,11 +364,12 @@ __global__ void __launch_bounds__(kHist4Threads, 1)
         atomicAdd(reinterpret_cast<unsigned *>(base + 98304 + (((o >> 17) & 0x7F80u) | lane4)), 1u);
     };
     const uintptr_t addr = (uintptr_t)keys;
-    size_t          head = ((16 - (addr & 15)) & 15) / 4;
+    size_t          head = pairs ? 0 : ((16 - (addr & 15)) & 15) / 4; // (a pair buffer is 16-byte aligned)
     if (head > n)
         head = n;
-    const size_t nvec   = (n - head) / 4;
-    const size_t tail   = head + nvec * 4;
+    const size_t per    = pairs ? 2 : 4; // keys per 16-byte vector
+    const size_t nvec   = (n - head) / per;
+    const size_t tail   = head + nvec * per;
     const uint4 *vin    = reinterpret_cast<const uint4 *>(keys + head);
     const size_t stride = (size_t)gridDim.x * kHist4Threads;
     size_t       v      = (size_t)blockIdx.x * kHist4Threads + threadIdx.x;
@@ -377,23 +381,27 @@ __global__ void __launch_bounds__(kHist4Threads, 1)
 #pragma unroll
         for (int k = 0; k < 4; k++) {
             count(r[k].x);
-            count(r[k].y);
+            if (!pairs)
+                count(r[k].y);
             count(r[k].z);
-            count(r[k].w);
+            if (!pairs)
+                count(r[k].w);
         }
     }
     for (; v < nvec; v += stride) {
         uint4 r = ld_stream_u4(vin + v);
         count(r.x);
-        count(r.y);
+        if (!pairs)
+            count(r.y);
         count(r.z);
-        count(r.w);
+        if (!pairs)
+            count(r.w);
     }
     if (blockIdx.x == 0) {
         for (size_t i = threadIdx.x; i < head; i += kHist4Threads)
             count(keys[i]);
         for (size_t i = tail + threadIdx.x; i < n; i += kHist4Threads)
-            count(keys[i]);
+            count(keys[pairs ? 2 * i : i]);
     }
     __syncthreads();
     // fold the lane columns: 1024 rows, 32 per warp; lane r keeps row warp*32 + r
@@ -702,15 +710,82 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
 #define SORT_PAIR_AT(j) const unsigned x = S.buf[j], y = S.vbuf[j]
 #endif
     if constexpr (kPeer) {
+        if (peer.v[0] == 0ull && peer.bulk) {
+            // Pair-format receive buffers, runs sent by the bulk-copy engine (cp.async.bulk shared -> peer global): the
+            // stores of a tile no longer sit in the LSU queue in front of the other CTA's shared-memory traffic while
+            // NVLink pushes back, and the CTA's warps are free the moment the copies are issued.  A bulk copy wants
+            // 16-byte alignment on both sides and a pair has 8 bytes: the runs are re-spaced in shared memory (at most
+            // one slot in front of each bucket) so that a run's slot has the parity of its index in the receive buffer;
+            // an odd first / last pair travels as an ordinary 8-byte store.
+            const unsigned nb = nspl + 1;
+            if (tid == 0) {
+                unsigned p = 0;
+                for (unsigned d = 0; d < nb; d++) {
+                    p += (p + S.gofs[d]) & 1u; // slot tstart + p and index gofs + tstart: same parity
+                    S.respace[d] = p;
+                }
+            }
+            __syncthreads();
+            uint2    pr[kSortItems];
+            unsigned ns[kSortItems];
 #pragma unroll
-        for (int k = 0; k < kSortItems; k++) {
-            const unsigned j = tid + k * kSortThreads;
-            SORT_PAIR_AT(j);
-            const unsigned d = op(x); // bucket == destination rank
-            const unsigned g = S.gofs[d] + j;
-            if (j < valid) {
-                reinterpret_cast<unsigned *>(peer.k[d])[g] = x;
-                reinterpret_cast<unsigned *>(peer.v[d])[g] = y;
+            for (int k = 0; k < kSortItems; k++) {
+                const unsigned j = tid + k * kSortThreads;
+                pr[k]            = S.pair[j];
+                ns[k]            = j + S.respace[op(pr[k].x)];
+            }
+            __syncthreads(); // every slot has been read: the runs may move
+#pragma unroll
+            for (int k = 0; k < kSortItems; k++)
+                S.pair[ns[k]] = pr[k];
+            fence_proxy_async_smem(); // the copy engine reads what the threads wrote
+            __syncthreads();
+            if (tid < nb) {
+                const unsigned d = tid;
+                unsigned       c = S.cnt[d];
+                if (d == nb - 1)
+                    c -= kSortTile - valid; // the pads of a ragged last tile close the last bucket's run
+                unsigned s = S.tstart[d] + S.respace[d];
+                unsigned g = S.gofs[d] + S.tstart[d];
+                uint2   *q = reinterpret_cast<uint2 *>(peer.k[d]);
+                if (c && (g & 1u)) {
+                    q[g] = S.pair[s];
+                    s++, g++, c--;
+                }
+                unsigned body = c & ~1u;
+                if (c & 1u)
+                    q[g + body] = S.pair[s + body];
+                while (body) { // 16 KiB per copy
+                    const unsigned m = body < 2048u ? body : 2048u;
+                    bulk_s2g(q + g, &S.pair[s], m * 8u);
+                    s += m, g += m, body -= m;
+                }
+                bulk_commit();
+                bulk_wait_all<0>(); // written, not just read: the kernel's end is what the barrier kernel relies on
+            }
+        }
+        else if (peer.v[0] == 0ull) { // pair-format receive buffers: half the store instructions, runs twice as long
+#pragma unroll
+            for (int k = 0; k < kSortItems; k++) {
+                const unsigned j = tid + k * kSortThreads;
+                SORT_PAIR_AT(j);
+                const unsigned d = op(x); // bucket == destination rank
+                const unsigned g = S.gofs[d] + j;
+                if (j < valid)
+                    reinterpret_cast<uint2 *>(peer.k[d])[g] = make_uint2(x, y);
+            }
+        }
+        else {
+#pragma unroll
+            for (int k = 0; k < kSortItems; k++) {
+                const unsigned j = tid + k * kSortThreads;
+                SORT_PAIR_AT(j);
+                const unsigned d = op(x);
+                const unsigned g = S.gofs[d] + j;
+                if (j < valid) {
+                    reinterpret_cast<unsigned *>(peer.k[d])[g] = x;
+                    reinterpret_cast<unsigned *>(peer.v[d])[g] = y;
+                }
             }
         }
     }
@@ -808,6 +883,7 @@ constexpr size_t kSortOffHist = 16, kSortOffTickets = 16 + 4 * kRadix * 4, kSort
 static_assert(kSortOffDesc % 16 == 0, "descriptor rows are zeroed with 16-byte stores");
 
 static int g_sort_lb = 4; // look-back descriptors fetched per round trip (1, 4 or 8)
+static bool g_sort_peer_bulk = true; // peer partition pass (pair format): cp.async.bulk shared -> peer global
 static bool g_sort_pairs = true; // intermediate results as (key, value) pairs in library-owned buffers (2 x 8N bytes)
 constexpr size_t kSortPairsMin = 1u << 16;
 
@@ -891,10 +967,28 @@ static int sort_kv(uint32_t *d_dstKey, uint32_t *d_dstVal, uint32_t *d_bufKey, u
         if (grid < 1)
             grid = 1;
         sort_hist4_kernel<<<grid, kHist4Threads, 4 * kRadix * 32 * 4, stream>>>(
-            d_srcKey, N, flip, ghist, hticket, d_n, reinterpret_cast<uint4 *>(base + kSortOffDesc), 4 * desc_bytes / 16);
+            d_srcKey, N, flip, ghist, hticket, d_n, reinterpret_cast<uint4 *>(base + kSortOffDesc), 4 * desc_bytes / 16,
+            d_srcVal == nullptr);
         B200_TRY(cudaGetLastError());
     }
 
+    if (d_srcVal == nullptr) {
+        // the input IS a pair buffer (the receive buffer of the sharded sort): every pass reads pairs
+        B200_TRY((cudaError_t)ensure(c->sort_pairs, 2 * N * sizeof(uint2), stream));
+        uint2 *P0 = reinterpret_cast<uint2 *>(c->sort_pairs.ptr), *P1 = P0 + N;
+        auto   gb = [&](int p) { return (const unsigned *)(ghist + p * kRadix); };
+        auto   ds = [&](int p) { return reinterpret_cast<unsigned *>(base + kSortOffDesc + p * desc_bytes); };
+        B200_TRY((cudaError_t)launch_pass_io<2>(tiles, stream, d_srcKey, nullptr, P0, nullptr, (unsigned)N, 0u, flip,
+                                                gb(0), tickets + 0, ds(0), d_n));
+        B200_TRY((cudaError_t)launch_pass_io<2>(tiles, stream, P0, nullptr, P1, nullptr, (unsigned)N, 8u, flip, gb(1),
+                                                tickets + 1, ds(1), d_n));
+        B200_TRY((cudaError_t)launch_pass_io<2>(tiles, stream, P1, nullptr, P0, nullptr, (unsigned)N, 16u, flip, gb(2),
+                                                tickets + 2, ds(2), d_n));
+        B200_TRY((cudaError_t)launch_pass_io<3>(tiles, stream, P0, nullptr, d_dstKey, d_dstVal, (unsigned)N, 24u, flip,
+                                                gb(3), tickets + 3, ds(3), d_n));
+        count_launch(5);
+        return 0;
+    }
     if (g_sort_pairs && g_sort_lb == 4 && N >= kSortPairsMin) {
         // src -> P0 -> P1 -> P0 -> dst with the three intermediate results as (key, value) pairs in library scratch
         if (ensure(c->sort_pairs, 2 * N * sizeof(uint2), stream) == 0) {
@@ -1044,9 +1138,10 @@ extern "C" int b200_partition_exchange_kv_async(const uint32_t *d_srcKey, const 
     SortPeer sp;
     for (int r = 0; r < kP2PMaxRanks; r++) {
         sp.k[r] = r < (int)world ? (unsigned long long)(uintptr_t)recvKeys[r] : 0ull;
-        sp.v[r] = r < (int)world ? (unsigned long long)(uintptr_t)recvVals[r] : 0ull;
+        sp.v[r] = (r < (int)world && recvVals) ? (unsigned long long)(uintptr_t)recvVals[r] : 0ull;
     }
     sp.info = d_info;
+    sp.bulk = g_sort_peer_bulk ? 1u : 0u;
     B200_TRY((cudaError_t)opt_in_smem(c, kAttrSortPeer, sort_pass_kernel<true, 4, true>, sizeof(SortSmem)));
     // N == 0: one CTA that only takes part in the closing exchange
     sort_pass_kernel<true, 4, true><<<tiles ? tiles : 1, kSortThreads, sizeof(SortSmem), stream>>>(
@@ -1059,6 +1154,11 @@ extern "C" int b200_partition_exchange_kv_async(const uint32_t *d_srcKey, const 
     return b200_p2p_barrier_async(stream_);
 }
 
+extern "C" int b200_tune_sort_peer_bulk(int on)
+{
+    g_sort_peer_bulk = on != 0;
+    return 0;
+}
 extern "C" int b200_tune_sort_pairs(int on)
 {
     g_sort_pairs = on != 0;
@@ -1081,7 +1181,7 @@ extern "C" int b200_sort_reserve(size_t N)
         return st;
     const size_t tiles = (N + kSortTile - 1) / kSortTile;
     B200_TRY((cudaError_t)ensure(c->sort, kSortOffDesc + 4 * tiles * kRadix * 4, 0));
-    if (g_sort_pairs && N >= kSortPairsMin)
+    if (g_sort_pairs) // (also what a pair-format input needs, whatever its size)
         B200_TRY((cudaError_t)ensure(c->sort_pairs, 2 * N * sizeof(uint2), 0));
     B200_TRY((cudaError_t)opt_in_smem(c, kAttrMisc0, sort_pass_kernel<false, 4, false, 1>, sizeof(SortSmem)));
     B200_TRY((cudaError_t)opt_in_smem(c, kAttrMisc1, sort_pass_kernel<false, 4, false, 2>, sizeof(SortSmem)));
@@ -1124,6 +1224,9 @@ int sort_preload()
     B200_TRY((cudaError_t)opt_in_smem(c, kAttrSortPass1, sort_pass_kernel<false, 4>, sizeof(SortSmem)));
     B200_TRY((cudaError_t)opt_in_smem(c, kAttrSortPass0, sort_pass_kernel<false, 1>, sizeof(SortSmem)));
     B200_TRY((cudaError_t)opt_in_smem(c, kAttrSortPass2, sort_pass_kernel<false, 8>, sizeof(SortSmem)));
+    B200_TRY((cudaError_t)opt_in_smem(c, kAttrMisc0, sort_pass_kernel<false, 4, false, 1>, sizeof(SortSmem)));
+    B200_TRY((cudaError_t)opt_in_smem(c, kAttrMisc1, sort_pass_kernel<false, 4, false, 2>, sizeof(SortSmem)));
+    B200_TRY((cudaError_t)opt_in_smem(c, kAttrMisc2, sort_pass_kernel<false, 4, false, 3>, sizeof(SortSmem)));
     return 0;
 }
 } // namespace b200

@@ -23,6 +23,9 @@
 #ifndef B200_SCAN_LOAD_EVICT_FIRST
 #define B200_SCAN_LOAD_EVICT_FIRST 0
 #endif
+#ifndef B200_SCAN_RELOAD_HINTS
+#define B200_SCAN_RELOAD_HINTS 0
+#endif
 #ifndef B200_SCAN_STORE_EVICT_FIRST
 #define B200_SCAN_STORE_EVICT_FIRST 0
 #endif
@@ -494,6 +497,11 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
             mbar_expect_tx(&S.full[s], count * 4u);
 #if B200_SCAN_LOAD_EVICT_FIRST
             bulk_g2s_hint(S.buf[s], src + off, count * 4u, &S.full[s], kL2EvictFirst);
+#elif B200_SCAN_RELOAD_HINTS
+            if (kReload) // the tile is read again in a few microseconds: keep it
+                bulk_g2s_hint(S.buf[s], src + off, count * 4u, &S.full[s], kL2EvictLast);
+            else
+                bulk_g2s(S.buf[s], src + off, count * 4u, &S.full[s]);
 #else
             bulk_g2s(S.buf[s], src + off, count * 4u, &S.full[s]);
 #endif
@@ -593,7 +601,11 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
 #pragma unroll
             for (int r = 0; r < kTmaRows; r++) {
                 const unsigned e = warp * (kTmaRows * 128) + r * 128 + lane * 4;
-                v[r]             = e < count ? ld_once_u4(in + e) : make_uint4(0, 0, 0, 0);
+#if B200_SCAN_RELOAD_HINTS
+                v[r] = e < count ? ld_once_hint_u4(in + e, kL2EvictFirst) : make_uint4(0, 0, 0, 0); // last use
+#else
+                v[r] = e < count ? ld_once_u4(in + e) : make_uint4(0, 0, 0, 0);
+#endif
             }
         };
         const bool early = kReload && b < a;
@@ -748,7 +760,7 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
             o.z += v[r].z & p.incl;
             o.w += v[r].w & p.incl;
             if (ebase[r] < count) {
-#if B200_SCAN_STORE_EVICT_FIRST
+#if B200_SCAN_STORE_EVICT_FIRST || B200_SCAN_RELOAD_HINTS
                 st_stream_hint_u4(out + ebase[r], o, kL2EvictFirst);
 #else
                 st_stream_u4(out + ebase[r], o);
@@ -771,7 +783,11 @@ using namespace b200;
 #ifndef B200_SCAN_RELOAD_AHEAD
 #define B200_SCAN_RELOAD_AHEAD 6
 #endif
-static bool g_scan_reload = false; // long arrays: stages hold a tile for its landing time only, phase B re-reads it from L2
+// Reload pipeline (stage freed after phase A, phase B re-reads the tile with 16-byte loads): measured and NOT used
+// (profiles/r02u_scan_reload_*.log, one 2^28 array): 391 us for tiles that wait in shared memory against 467 / 427 /
+// 484 us with 2 / 3 / 6 tiles of look-ahead; ncu at 3: the second read hits L2 for 73 % of its sectors only (DRAM
+// reads 1.27 GB instead of 1.07 GB) and eviction hints change nothing.  Kept behind the knob for the record.
+static bool g_scan_reload = false;
 extern "C" int b200_tune_scan_reload(int on)
 {
     g_scan_reload = on != 0;

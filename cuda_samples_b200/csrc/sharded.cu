@@ -39,7 +39,9 @@ struct b200_ctx {
     uint32_t *meta[kP2PMaxRanks];   // [0, w*w) count matrix | [w*w] pairs received | [w*w+1] overflow | splitters | carry
     // receive buffers + ping-pong scratch of the sharded sort (grow-only)
     size_t    capacity = 0;
-    uint32_t *recvK[kP2PMaxRanks], *recvV[kP2PMaxRanks], *bufK[kP2PMaxRanks], *bufV[kP2PMaxRanks];
+    // (several devices: one pair-format receive buffer each, 8 bytes per pair -- the partition pass stores (key, value)
+    // with ONE peer store and the local sort reads pairs; one device: the ping-pong arrays b200_sort_kv_async wants)
+    uint32_t *recvP[kP2PMaxRanks], *bufK[kP2PMaxRanks], *bufV[kP2PMaxRanks];
     // pinned host staging for results
     double   *h_work = nullptr;     // [ndev][4]
     uint32_t *h_meta = nullptr;     // [ndev][w*w + 2]
@@ -85,7 +87,7 @@ int free_sort_buffers(b200_ctx *c)
 {
     for (int i = 0; i < c->ndev; i++) {
         B200_TRY(cudaSetDevice(c->dev[i]));
-        for (uint32_t **p : {&c->recvK[i], &c->recvV[i], &c->bufK[i], &c->bufV[i]}) {
+        for (uint32_t **p : {&c->recvP[i], &c->bufK[i], &c->bufV[i]}) {
             if (*p)
                 B200_TRY(cudaFree(*p));
             *p = nullptr;
@@ -101,11 +103,12 @@ int reserve_sort(b200_ctx *c, size_t capacity, size_t max_n)
         B200_TRY((cudaError_t)free_sort_buffers(c));
         for (int i = 0; i < c->ndev; i++) {
             B200_TRY(cudaSetDevice(c->dev[i]));
-            for (uint32_t **p : {&c->recvK[i], &c->recvV[i], &c->bufK[i], &c->bufV[i]}) {
-                if (c->ndev == 1 && (p == &c->recvK[i] || p == &c->recvV[i]))
-                    continue; // one device: nothing is exchanged
-                B200_TRY(cudaMalloc(p, capacity * sizeof(uint32_t)));
+            if (c->ndev == 1) { // one device: nothing is exchanged
+                B200_TRY(cudaMalloc(&c->bufK[i], capacity * sizeof(uint32_t)));
+                B200_TRY(cudaMalloc(&c->bufV[i], capacity * sizeof(uint32_t)));
             }
+            else
+                B200_TRY(cudaMalloc(&c->recvP[i], capacity * 2 * sizeof(uint32_t)));
         }
         c->capacity = capacity;
     }
@@ -136,7 +139,7 @@ extern "C" int b200_ctx_create(int ndev, const int *devices, b200_ctx **out)
         c->stream[i] = nullptr;
         c->work[i]   = nullptr;
         c->meta[i]   = nullptr;
-        c->recvK[i] = c->recvV[i] = c->bufK[i] = c->bufV[i] = nullptr;
+        c->recvP[i] = c->bufK[i] = c->bufV[i] = nullptr;
     }
     int st = p2p_connect_local(ndev, devices);
     if (st) {
@@ -352,23 +355,20 @@ extern "C" int b200_sort_kv_sharded(b200_ctx *c, uint32_t *const *d_dstKey, uint
     }
     // 2. count + exchange of counts, stable partition whose bucket runs are stored straight into the destination
     //    device's receive buffer over NVLink, node-wide barrier
-    void *rk[kP2PMaxRanks], *rv[kP2PMaxRanks];
-    for (int i = 0; i < w; i++) {
-        rk[i] = c->recvK[i];
-        rv[i] = c->recvV[i];
-    }
+    void *rp[kP2PMaxRanks];
+    for (int i = 0; i < w; i++)
+        rp[i] = c->recvP[i];
     for (int i = 0; i < w; i++) {
         B200_TRY(cudaSetDevice(c->dev[i]));
         B200_TRY((cudaError_t)b200_partition_exchange_kv_async(d_srcKey[i], d_srcVal[i], n[i], meta_splitters(c, i),
-                                                               sortDir, rk, rv, cap, meta_matrix(c, i), meta_info(c, i),
+                                                               sortDir, rp, nullptr, cap, meta_matrix(c, i), meta_info(c, i),
                                                                (b200_stream_t)c->stream[i]));
     }
     // 3. local stable sort of what arrived, count read on the device
     for (int i = 0; i < w; i++) {
         B200_TRY(cudaSetDevice(c->dev[i]));
-        B200_TRY((cudaError_t)b200_sort_kv_dyn_async(d_dstKey[i], d_dstVal[i], c->bufK[i], c->bufV[i], c->recvK[i],
-                                                     c->recvV[i], cap, meta_info(c, i), sortDir,
-                                                     (b200_stream_t)c->stream[i]));
+        B200_TRY((cudaError_t)b200_sort_kv_dyn_async(d_dstKey[i], d_dstVal[i], nullptr, nullptr, c->recvP[i], nullptr,
+                                                     cap, meta_info(c, i), sortDir, (b200_stream_t)c->stream[i]));
         B200_TRY(cudaMemcpyAsync(c->h_meta + (size_t)i * (kP2PMaxRanks * kP2PMaxRanks + 2), c->meta[i],
                                  (w * w + 2) * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream[i]));
     }

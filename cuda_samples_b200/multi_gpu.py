@@ -51,14 +51,12 @@ def disable_p2p(group=None):
         torch.cuda.synchronize()
         dist.barrier(group=group)
         for b in _RECV.values():
-            for r, (k, v) in enumerate(zip(b["keys"], b["vals"])):
+            for r, q in enumerate(b["pairs"]):
                 if r != b["rank"]:
-                    api.p2p_buffer_close(k)
-                    api.p2p_buffer_close(v)
+                    api.p2p_buffer_close(q)
         dist.barrier(group=group)
         for b in _RECV.values():
-            api.p2p_buffer_free(b["keys"][b["rank"]])
-            api.p2p_buffer_free(b["vals"][b["rank"]])
+            api.p2p_buffer_free(b["pairs"][b["rank"]])
         _RECV.clear()
         api.p2p_disconnect()
         _P2P["world"] = 0
@@ -76,13 +74,11 @@ def _recv_buffers(n_local, factor, rank, world, group):
         biggest = torch.tensor([n_local], dtype=torch.int64, device="cuda")
         dist.all_reduce(biggest, op=dist.ReduceOp.MAX, group=group)
         capacity = (int(int(biggest.item()) * factor) + 2 * 8192 - 1) // 8192 * 8192
-        kp, kh = api.p2p_buffer_create(4 * capacity)
-        vp, vh = api.p2p_buffer_create(4 * capacity)
+        pp, ph = api.p2p_buffer_create(8 * capacity)  # (key, value) pairs: one 8-byte peer store per pair
         handles = [None] * world
-        dist.all_gather_object(handles, (kh, vh), group=group)
+        dist.all_gather_object(handles, ph, group=group)
         b = {"rank": rank, "capacity": capacity,
-             "keys": [kp if r == rank else api.p2p_buffer_open(handles[r][0]) for r in range(world)],
-             "vals": [vp if r == rank else api.p2p_buffer_open(handles[r][1]) for r in range(world)]}
+             "pairs": [pp if r == rank else api.p2p_buffer_open(handles[r]) for r in range(world)]}
         dist.barrier(group=group)
         _RECV[key] = b
     return b
@@ -292,7 +288,7 @@ def sort_exchange_only(keys, vals, n_local, direction=1, group=None, capacity_fa
         sort_sharded(keys, vals, n_local, direction, group=group, capacity_factor=capacity_factor)
     w = b["work"]
     api.sort_splitters(keys, n_local, direction, w["spl"])
-    api.partition_exchange_kv(keys, vals, n_local, w["spl"], direction, b["keys"], b["vals"], b["capacity"],
+    api.partition_exchange_kv(keys, vals, n_local, w["spl"], direction, b["pairs"], None, b["capacity"],
                               w["meta"][:world * world], w["meta"][world * world:])
     return w["meta"]
 
@@ -302,8 +298,8 @@ def nvlink_probe(src, nbytes, n_local, group=None, capacity_factor=1.25):
     (rank+1) % world at the same time.  -> {mode name: GB/s per direction per GPU on this rank}."""
     rank, world = _world(group)
     b = _recv_buffers(n_local, capacity_factor, rank, world, group)
-    peer = b["keys"][(rank + 1) % world]
-    nbytes = min(nbytes, 4 * b["capacity"])
+    peer = b["pairs"][(rank + 1) % world]
+    nbytes = min(nbytes, 8 * b["capacity"])
     out = {}
     for mode, name in ((3, "cudaMemcpyAsync"), (1, "16-byte lane stores"), (0, "4-byte lane stores"),
                        (2, "cp.async.bulk from shared memory")):
@@ -348,8 +344,7 @@ def sort_sharded(keys, vals, n_local, direction=1, ops=None, group=None, samples
         cap = b["capacity"]
         if "work" not in b:  # per-shape work buffers live with the receive buffers: nothing is allocated per call
             mk = lambda n: torch.empty(n, dtype=torch.int32, device=keys.device)  # noqa: E731
-            b["work"] = {"spl": mk(max(world - 1, 1)), "meta": mk(world * world + 2), "dk": mk(cap), "dv": mk(cap),
-                         "bk": mk(cap), "bv": mk(cap)}
+            b["work"] = {"spl": mk(max(world - 1, 1)), "meta": mk(world * world + 2), "dk": mk(cap), "dv": mk(cap)}
             api.sort_reserve(max(cap, n_local))  # library scratch too: no allocation between kernels that wait on peers
             torch.cuda.synchronize()
             dist.barrier(group=group)
@@ -358,11 +353,10 @@ def sort_sharded(keys, vals, n_local, direction=1, ops=None, group=None, samples
         # 1. splitters on the device: regular samples -> peer windows -> bitonic sort -> same splitters everywhere
         api.sort_splitters(keys, n_local, direction, spl)
         # 2-4 fused: count + exchange of counts, partition pass that scatters into the peers' receive buffers
-        api.partition_exchange_kv(keys, vals, n_local, spl, direction, b["keys"], b["vals"], cap,
+        api.partition_exchange_kv(keys, vals, n_local, spl, direction, b["pairs"], None, cap,
                                   meta[:world * world], meta[world * world:])
-        # 5. local stable sort of the receive buffer, received count read on the device: no host round trip
-        api.sort_kv_dyn(w["dk"], w["dv"], w["bk"], w["bv"], b["keys"][rank], b["vals"][rank], cap,
-                        meta[world * world:], direction)
+        # 5. local stable sort of the (pair-format) receive buffer, received count read on the device: no host round trip
+        api.sort_kv_dyn(w["dk"], w["dv"], None, None, b["pairs"][rank], None, cap, meta[world * world:], direction)
         if not sync:
             return w["dk"], w["dv"], meta, None
         host = meta.cpu()  # the only synchronisation: after everything is queued

@@ -93,7 +93,9 @@ int b200_integral_image_u8_async(uint32_t *d_out, const uint8_t *d_img, size_t w
 
 /* sort: replaces mergeSort() (mergeSort.cu:471-537): STABLE key-value sort, sortDir != 0 ascending,
  * == 0 descending, ties keep source order.  Result in dst, buf is scratch, src is left untouched.
- * Any N >= 0 (the sample asserts N % 1024 == 0 and N <= 2^22).  src may not alias dst/buf. */
+ * Any N >= 0 (the sample asserts N % 1024 == 0 and N <= 2^22).  src may not alias dst/buf.
+ * d_srcVal == NULL: d_srcKey is an array of N interleaved (key, value) pairs (8 bytes each, 16-byte aligned) -- the
+ * format of the sharded sort's receive buffers; buf is then unused and may be NULL. */
 int b200_sort_kv_async(uint32_t *d_dstKey, uint32_t *d_dstVal, uint32_t *d_bufKey, uint32_t *d_bufVal,
                        const uint32_t *d_srcKey, const uint32_t *d_srcVal, size_t N, uint32_t sortDir,
                        b200_stream_t stream);
@@ -164,6 +166,8 @@ int b200_sort_kv_dyn_async(uint32_t *d_dstKey, uint32_t *d_dstVal, uint32_t *d_b
 /* partition + all-to-all of the multi-GPU sample sort without a collective call: bucket b == rank b, the stable
  * partition pass stores every bucket's run straight into rank b's receive buffer over NVLink.  recvKeys/recvVals:
  * HOST arrays of `world` device pointers (rank r's receive buffer as mapped here), `capacity` pairs each.
+ * recvVals == NULL: recvKeys[r] are PAIR buffers (8 * capacity bytes): one 8-byte peer store per pair; sort them with
+ * b200_sort_kv_dyn_async(..., d_srcKey = the own pair buffer, d_srcVal = NULL, ...).
  * d_matrix [world][world]
  * (row = source rank), d_info[0] = pairs received, d_info[1] != 0: a buffer would overflow, nothing was sent. */
 int b200_partition_exchange_kv_async(const uint32_t *d_srcKey, const uint32_t *d_srcVal, size_t N,
@@ -242,6 +246,9 @@ int b200_host_alloc_info(const void *h_ptr, int *gpu_node, int *mem_node_first, 
  * h_src to device memory between events, best of `reps`, in GB/s (method of the reference's
  * 5_Domain_Specific/p2pBandwidthLatencyTest/p2pBandwidthLatencyTest.cu:113-146) */
 int b200_host_probe_h2d(const void *h_src, size_t bytes, int reps, double *best_gbs);
+/* reps back-to-back copies of the pinned buffer into d_dst; *seconds = first copy issued -> last copy complete.  Called
+ * by every rank between the same two barriers it measures what the host can feed all GPUs at once. */
+int b200_host_probe_h2d_sustained(void *d_dst, const void *h_src, size_t bytes, int reps, double *seconds);
 
 #ifdef __cplusplus
 }

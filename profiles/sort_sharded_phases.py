@@ -15,6 +15,8 @@ rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int
 torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 mg.enable_p2p()
+if os.environ.get("SORT_PEER_BULK"):  # 0: 8-byte lane stores into the peers' pair buffers, 1: cp.async.bulk from shared memory
+    prim.lib.b200_tune_sort_peer_bulk(int(os.environ["SORT_PEER_BULK"]))
 n = (1 << 28) // world
 sk = torch.empty(n, dtype=torch.int32, device="cuda")
 sv = torch.arange(rank * n, rank * n + n, dtype=torch.int64, device="cuda").to(torch.int32)
@@ -35,12 +37,12 @@ for _ in range(REPS):
     api.sort_splitters(sk, n, 1, spl)  # jittered samples -> peer windows -> bitonic sort -> the same splitters everywhere
     ev[1].record()
     meta = torch.empty(world * world + 2, dtype=torch.int32, device="cuda")
-    api.partition_exchange_kv(sk, sv, n, spl, 1, b["keys"], b["vals"], cap, meta[:world * world], meta[world * world:])
+    api.partition_exchange_kv(sk, sv, n, spl, 1, b["pairs"], None, cap, meta[:world * world], meta[world * world:])
     ev[2].record()
     w = b["work"]
-    dk, dv, bk, bv = w["dk"], w["dv"], w["bk"], w["bv"]
+    dk, dv = w["dk"], w["dv"]
     ev[3].record()
-    api.sort_kv_dyn(dk, dv, bk, bv, b["keys"][rank], b["vals"][rank], cap, meta[world * world:], 1)
+    api.sort_kv_dyn(dk, dv, None, None, b["pairs"][rank], None, cap, meta[world * world:], 1)
     ev[4].record()
     host = meta.cpu()
     ev[5].record()

@@ -789,6 +789,36 @@ def test_sort_with_device_side_count(prim):
             assert bool((dk[n:] == -7).all()), "nothing beyond the counted pairs may be written"
 
 
+def test_sort_from_a_pair_buffer(prim):
+    """d_srcVal == NULL: the input is an array of interleaved (key, value) pairs -- the format of the sharded sort's
+    receive buffers (one 8-byte peer store per pair).  Every pass then reads pairs; the result is the usual split
+    dst arrays, the count may come from the device, and the pair buffer itself stays untouched."""
+    rng = np.random.default_rng(23)
+    cap = (1 << 17) + 8192 + 6
+    keys = rng.integers(0, 1 << 32, cap, dtype=np.uint64).astype(np.uint32)
+    keys[: cap // 2] &= 0xFFFF  # ties: stability matters
+    vals = rng.integers(0, 1 << 32, cap, dtype=np.uint64).astype(np.uint32)
+    pairs = np.empty(2 * cap, np.uint32)
+    pairs[0::2], pairs[1::2] = keys, vals
+    sp = dev(pairs.view(np.int32))
+    for n in (0, 1, 2, 3, 8191, 8193, 70001, cap):
+        for direction in (1, 0):
+            dk, dv = (torch.full((cap,), -7, dtype=torch.int32, device="cuda") for _ in range(2))
+            d_n = torch.tensor([n, 0], dtype=torch.int32, device="cuda")
+            prim.sort_kv_dyn(dk, dv, None, None, sp, None, cap, d_n, direction)
+            wk, wv = oracle.stable_sort_kv(keys[:n], vals[:n], direction)
+            assert (dk[:n].cpu().numpy().view(np.uint32) == wk).all(), (n, direction)
+            assert (dv[:n].cpu().numpy().view(np.uint32) == wv).all(), (n, direction)
+            assert bool((dk[n:] == -7).all()) and bool((dv[n:] == -7).all())
+    assert (sp.cpu().numpy().view(np.uint32) == pairs).all()
+    # host-known count through the plain entry point
+    n = 100003
+    dk, dv = (torch.empty(n, dtype=torch.int32, device="cuda") for _ in range(2))
+    prim.mergeSort(dk, dv, None, None, sp, None, n, 1)
+    wk, wv = oracle.stable_sort_kv(keys[:n], vals[:n], 1)
+    assert (dk.cpu().numpy().view(np.uint32) == wk).all() and (dv.cpu().numpy().view(np.uint32) == wv).all()
+
+
 def test_peer_window_entry_points_world_1(prim):
     """The fused compute + exchange kernels with a one-rank window set: same results as the plain kernels
     (the 2/4/8-GPU case is tests/multi_gpu_check.py)."""
