@@ -571,7 +571,7 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
                     prefix = sum2 + sum1;
                 }
                 if (lane == 0) {
-                    SCAN_TRACE_VAL(tile, 4, polls + 1);
+                    SCAN_TRACE_VAL(tile, 4, (unsigned long long)(polls + 1) | ((unsigned long long)blockIdx.x << 32));
                     st_relaxed_u64(desc + tile, make_desc(epoch, kStP, prefix + aggregate));
                     if (closes)
                         st_relaxed_u64(cdesc + chunk, make_desc(epoch, kStP, prefix + aggregate));
@@ -643,6 +643,8 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
             }
             const unsigned count = S.count[m];
             unsigned       sum   = 0;
+            if (threadIdx.x == 0)
+                SCAN_TRACE(tile, 1);
 #pragma unroll
             for (int r = 0; r < kTmaRows; r++) {
                 const unsigned e = warp * (kTmaRows * 128) + r * 128 + lane * 4;
@@ -679,6 +681,8 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
         const unsigned s = b % kTmaStages, m = b % kRing;
         if (kReload && !early)
             reload_tile();
+        if (threadIdx.x == 0)
+            SCAN_TRACE(S.tile[m], 7);
         mbar_wait(&S.prefix_ready[m], (b / kRing) & 1);
         const unsigned count = S.count[m];
         if (threadIdx.x == 0)
