@@ -378,6 +378,11 @@ __device__ __forceinline__ bool window32(const unsigned long long *desc, long lo
 // one 2^28-element array (profiles/r01_scan_geometry_sweep.log): 24 KiB x 9 stages 520 us, 32 KiB x 6 434 us,
 // 40 KiB x 5 (phase A 3 ahead) 395 us, 48 KiB x 4 413 us, 64 KiB x 3 477 us.  Short arrays (a few tiles each)
 // prefer 32 KiB tiles that divide them evenly (16384 arrays of 16384: 344 us vs 396 us).
+#ifndef B200_COMPACT_INPLACE
+#define B200_COMPACT_INPLACE 0 // compaction: the warp's rows of the stage double as its packing slab (see phase B);
+                               // measured equal (profiles/r02x_compact_inplace.log: 399 vs 401 us at 80 % kept, 357 vs
+                               // 362 at 50 %): the pipeline's tile period is set by stage residency, not by this loop
+#endif
 #ifndef B200_SCAN_EAGER_B
 #define B200_SCAN_EAGER_B 0 // measured: 410 vs 396 us for one 2^28 array (phase A falls behind, look-backs get longer)
 #endif
@@ -723,6 +728,44 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
         __syncwarp();
         if (threadIdx.x == 0)
             SCAN_TRACE(tile_b, 6);
+#if B200_COMPACT_INPLACE
+        if (kCompact) {
+            // The warp's own rows of the stage (all in registers now) are the packing slab for the WHOLE tile slice:
+            // one pass of shared stores, one __syncwarp, then the kept elements leave as full 128-byte store
+            // instructions -- two warp barriers per tile instead of two per row, and the loads of all the output
+            // instructions in flight together.  The stage goes back to the producer when the slab has been read.
+            unsigned *slab    = &S.buf[s][warp * (kTmaRows * 128)];
+            unsigned  rowbase = 0;
+#pragma unroll
+            for (int r = 0; r < kTmaRows; r++) {
+                unsigned pos = rowbase + inc[r] - tot[r];
+                if ((int)v[r].x > 0)
+                    slab[pos++] = v[r].x;
+                if ((int)v[r].y > 0)
+                    slab[pos++] = v[r].y;
+                if ((int)v[r].z > 0)
+                    slab[pos++] = v[r].z;
+                if ((int)v[r].w > 0)
+                    slab[pos++] = v[r].w;
+                rowbase += __shfl_sync(0xffffffffu, inc[r], 31);
+            }
+            __syncwarp();
+            unsigned t[kTmaRows * 4];
+#pragma unroll
+            for (int q = 0; q < kTmaRows * 4; q++)
+                t[q] = slab[q * 32 + lane];
+#pragma unroll
+            for (int q = 0; q < kTmaRows * 4; q++)
+                if (q * 32 + lane < rowbase)
+                    dst[run + q * 32 + lane] = t[q];
+            __syncwarp(); // (every lane's slab loads have been consumed by its stores)
+            if (lane == 0)
+                mbar_arrive(&S.scanned[s]);
+            if (tile_b == p.num_tiles - 1 && warp == kScanWarps - 1 && lane == 0)
+                *p.count_out = (int)(run + rowbase); // prefix + everything kept in the last tile
+            continue;
+        }
+#endif
         if (lane == 0)
             mbar_arrive(kReload ? &S.done[m] : &S.scanned[s]);
         const unsigned ab = tile_b / p.tpa;
