@@ -462,7 +462,17 @@ def primitives_table(torch, dist, prim, mg, rank, world, peak, barrier, p2p=Fals
         t3 = time_steps(torch, step_sort, 5, 2) / 5
         table["mergeSort_kv_2^28_keys_mod_65536"] = {
             "Gkeys/s": round(N_ELEMS / t3 / 1e9, 3), "ms_per_call": round(t3 * 1e3, 3), "n_gpus": 1,
+            "frac_of_measured_peak": round(36 * N_ELEMS / t3 / 1e9 / peak, 4),
+            "bytes_per_pair": "4 (digit histograms) + 2 x 16 (the two passes whose digit varies; the device-side "
+                              "pass plan skips the other two)",
             "dataset": "D3-like: key = counter-based random % 65536 (the sample's rand() % 65536 shape), ascending"}
+        # the sample's own size (mergeSort/main.cpp:46: N = 4 Mi pairs) with the same keys
+        m = 4 << 20
+        t4 = time_steps(torch, lambda: prim.mergeSort(dk[:m], dv[:m], bk[:m], bv[:m], sk[:m], sv[:m], m, 1), 50, 5) / 50
+        table["mergeSort_kv_4Mi_keys_mod_65536"] = {
+            "Gkeys/s": round(m / t4 / 1e9, 3), "us_per_call": round(t4 * 1e6, 1), "n_gpus": 1,
+            "dataset": "the sample's own shape: 4 Mi pairs, key = random % 65536, ascending (L2-resident: 32 MiB of "
+                       "pairs per buffer)"}
     if world == 1:
         # --- batched short-array sorts (sortingNetworks API): arrays <= 4096 pairs are sorted
         #     inside one CTA's shared memory: 16 B of traffic per pair.  Keys like the sample's (rand() % 65536).

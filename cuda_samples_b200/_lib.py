@@ -95,6 +95,7 @@ SIGNATURES = {
     "b200_tune_scan_backoff": (ci, [ci]),
     "b200_tune_sort_lookback": (ci, [ci]),
     "b200_tune_sort_pairs": (ci, [ci]),
+    "b200_tune_sort_plan": (ci, [ci]),
     "b200_tune_sort_peer_bulk": (ci, [ci]),
     "b200_tune_scan_reload": (ci, [ci]),
     # drop-in entry points (the samples' own signatures)

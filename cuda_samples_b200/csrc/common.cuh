@@ -68,7 +68,7 @@ enum FuncAttrBit : unsigned {
     kAttrSortHist4 = 1u << 4, kAttrSortPass0 = 1u << 5, kAttrSortPass1 = 1u << 6, kAttrSortPass2 = 1u << 7,
     kAttrSortPass3 = 1u << 8, kAttrSortPass4 = 1u << 9, kAttrSortPass5 = 1u << 10, kAttrSortPeer = 1u << 11,
     kAttrSegSort = 1u << 12, kAttrHist = 1u << 13, kAttrSortPassPk = 1u << 14, kAttrMisc0 = 1u << 15,
-    kAttrMisc1 = 1u << 16, kAttrMisc2 = 1u << 17, kAttrMisc3 = 1u << 18,
+    kAttrMisc1 = 1u << 16, kAttrMisc2 = 1u << 17, kAttrMisc3 = 1u << 18, kAttrSortPassDyn = 1u << 19,
 };
 template <typename K> inline int opt_in_smem(DeviceCtx *c, unsigned bit, K kernel, size_t bytes)
 {

@@ -108,6 +108,7 @@ struct SortPeer {
     unsigned           bulk;   // pair format only: runs leave through the bulk-copy engine instead of lane stores
 };
 struct NoPeer {};
+
 template <bool kPeer> struct PeerParam { typedef NoPeer type; };
 template <> struct PeerParam<true> { typedef SortPeer type; };
 
@@ -338,10 +339,56 @@ __global__ void __launch_bounds__(kSortThreads)
 // ---------------------------------------------------------------------------------------------------
 constexpr int kHist4Threads = 1024;
 
+// Pass plan of the four-pass sort, decided ON THE DEVICE by the last CTA of the histogram kernel: a pass whose digit
+// is the same for every key (one bin holds all n) is the identity permutation -- a stable partition of one class --
+// and is not run at all.  The mergeSort sample's own keys are rand() % 65536 (mergeSort/main.cpp:48,68): two of its
+// four passes are of that kind.  The passes that do run are chained on the fly: the first reads the caller's arrays,
+// the last writes the caller's dst, the ones in between alternate over the two pair buffers.
+// plan[p] = {skip, in_fmt, out_fmt, in_sel, out_sel, -, -, -}; fmt 0: split key / value arrays, 1: (key, value) pairs;
+// sel 0: caller's source, 1: pair buffer P0, 2: pair buffer P1, 3: caller's dst.
+struct SortPlanBufs {
+    const void *src_k, *src_v; // src_v == nullptr: the source is a pair buffer
+    void       *p0, *p1;
+    void       *dst_k, *dst_v;
+};
+__device__ __forceinline__ void make_sort_plan(unsigned *plan, const unsigned *trivial, bool src_pairs)
+{
+    int  first = -1, last = -1;
+    bool run[4];
+    for (int p = 0; p < 4; p++) {
+        run[p] = !trivial[p];
+        if (run[p]) {
+            if (first < 0)
+                first = p;
+            last = p;
+        }
+    }
+    if (first < 0) { // nothing to sort by: the last pass still moves the data from the source to dst (identity ranking)
+        run[3] = true;
+        first = last = 3;
+    }
+    unsigned cur = 0; // where the data is now (sel)
+    for (int p = 0; p < 4; p++) {
+        unsigned *q = plan + p * 8;
+        if (!run[p]) {
+            q[0] = 1;
+            continue;
+        }
+        const unsigned out = p == last ? 3u : (cur == 1u ? 2u : 1u);
+        q[0] = 0;
+        q[1] = cur == 0 ? (src_pairs ? 1u : 0u) : 1u;
+        q[2] = out == 3 ? 0u : 1u;
+        q[3] = cur;
+        q[4] = out;
+        cur  = out;
+    }
+}
+
 __global__ void __launch_bounds__(kHist4Threads, 1)
     sort_hist4_kernel(const unsigned *__restrict__ keys, size_t n, unsigned flip, unsigned *__restrict__ ghist,
                       unsigned *__restrict__ ticket, const unsigned *__restrict__ n_dev, uint4 *__restrict__ zero,
-                      size_t zero_vecs, bool pairs /* keys[2 i] is key i: the input is a (key, value) pair buffer */)
+                      size_t zero_vecs, bool pairs /* keys[2 i] is key i: the input is a (key, value) pair buffer */,
+                      unsigned *__restrict__ plan /* nullable: [4][8], see make_sort_plan */)
 {
     // the look-back descriptors of the four passes start at zero: stored from here (fire and forget, under the key
     // reads) instead of by a memset in front of the kernel
@@ -424,6 +471,21 @@ __global__ void __launch_bounds__(kHist4Threads, 1)
     if (!s_last)
         return;
     __threadfence();
+    if (plan) { // (before the counts become offsets) which passes have a single digit?
+        __shared__ unsigned s_trivial[4];
+        if (warp < 4) {
+            unsigned any = 0;
+#pragma unroll
+            for (int i = 0; i < 8; i++)
+                any |= (__ldcg(ghist + warp * kRadix + lane * 8 + i) == (unsigned)n) ? 1u : 0u;
+            any = __reduce_or_sync(0xffffffffu, any);
+            if (lane == 0)
+                s_trivial[warp] = any;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0)
+            make_sort_plan(plan, s_trivial, pairs);
+    }
     finish_digit_offsets(ghist, 4, nullptr, 0);
     if (threadIdx.x == 0)
         *ticket = 0;
@@ -449,15 +511,15 @@ __global__ void __launch_bounds__(kHist4Threads, 1)
 // layout); 1: separate in, interleaved (key, value) pairs out; 2: pairs in, pairs out; 3: pairs in, separate out.
 // The three intermediate results of a four-pass sort live in library-owned pair buffers: one 8-byte load and one 8-byte
 // store per pair instead of two of each, and a digit run is one contiguous 8 B x count segment.
-template <bool kBucket, int kLB, bool kPeer = false, int kIO = 0>
-__global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
-    sort_pass_kernel(const unsigned *__restrict__ kin, const unsigned *__restrict__ vin, unsigned *__restrict__ kout,
-                     unsigned *__restrict__ vout, unsigned n, unsigned shift, unsigned flip,
-                     const unsigned *__restrict__ splitters, unsigned nspl, const unsigned *__restrict__ gbase,
-                     unsigned *__restrict__ ticket, unsigned *__restrict__ desc, typename PeerParam<kPeer>::type peer,
-                     const unsigned *__restrict__ n_dev)
+template <bool kBucket, int kLB, bool kPeer, int kIO, bool kProlog = true>
+__device__ __forceinline__ void
+sort_pass_body(const unsigned *__restrict__ kin, const unsigned *__restrict__ vin, unsigned *__restrict__ kout,
+               unsigned *__restrict__ vout, unsigned n, unsigned shift, unsigned flip,
+               const unsigned *__restrict__ splitters, unsigned nspl, const unsigned *__restrict__ gbase,
+               unsigned *__restrict__ ticket, unsigned *__restrict__ desc, typename PeerParam<kPeer>::type peer,
+               const unsigned *__restrict__ n_dev)
 {
-    if (n_dev) { // device-side pair count: the grid covers the capacity, CTAs beyond the data leave at once
+    if (kProlog && n_dev) { // device-side pair count: the grid covers the capacity, CTAs beyond the data leave at once
         n = *n_dev < n ? *n_dev : n;
         if ((size_t)blockIdx.x * kSortTile >= n)
             return; // (tickets are only drawn by CTAs that have a tile: tiles stay dense in ticket order)
@@ -471,16 +533,16 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
             return;
     }
 
-    if (tid == 0)
-        S.tile = atomicAdd(ticket, 1u);
-    {
+    if (kProlog) { // (the planned kernel has done this already, under the load of its plan entry)
+        if (tid == 0)
+            S.tile = atomicAdd(ticket, 1u);
         uint4 *z = reinterpret_cast<uint4 *>(&S.wcnt[0][0]);
         for (int i = tid; i < kSortWarps * kRadix / 4; i += kSortThreads)
             z[i] = make_uint4(0u, 0u, 0u, 0u);
+        if (kBucket && tid < nspl)
+            S.splitters[tid] = splitters[tid];
+        __syncthreads();
     }
-    if (kBucket && tid < nspl)
-        S.splitters[tid] = splitters[tid];
-    __syncthreads();
     const unsigned   tile  = S.tile;
     SORT_TRACE(tile, 0);
     const unsigned   base  = tile * kSortTile;
@@ -824,6 +886,64 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
     }
 }
 
+template <bool kBucket, int kLB, bool kPeer = false, int kIO = 0>
+__global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
+    sort_pass_kernel(const unsigned *__restrict__ kin, const unsigned *__restrict__ vin, unsigned *__restrict__ kout,
+                     unsigned *__restrict__ vout, unsigned n, unsigned shift, unsigned flip,
+                     const unsigned *__restrict__ splitters, unsigned nspl, const unsigned *__restrict__ gbase,
+                     unsigned *__restrict__ ticket, unsigned *__restrict__ desc, typename PeerParam<kPeer>::type peer,
+                     const unsigned *__restrict__ n_dev)
+{
+    sort_pass_body<kBucket, kLB, kPeer, kIO>(kin, vin, kout, vout, n, shift, flip, splitters, nspl, gbase, ticket, desc,
+                                             peer, n_dev);
+}
+
+// A pass of the PLANNED four-pass sort: formats and buffers come from the device-side plan entry (make_sort_plan); a
+// skipped pass leaves at once; the others run one of the four statically specialised bodies (a CTA-uniform switch, so
+// each body keeps the register allocation and the code of its own kernel).
+__global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm)
+    sort_pass_plan_kernel(const unsigned *__restrict__ plan_entry, const SortPlanBufs B, unsigned n, unsigned shift,
+                          unsigned flip, const unsigned *__restrict__ gbase, unsigned *__restrict__ ticket,
+                          unsigned *__restrict__ desc, const unsigned *__restrict__ n_dev)
+{
+    // the plan entry is fetched UNDER the tile's prologue (ticket draw, counters zeroed): one L2 round trip, not two
+    const uint4    pl   = __ldg(reinterpret_cast<const uint4 *>(plan_entry));
+    const unsigned osel = __ldg(plan_entry + 4);
+    if (n_dev) {
+        n = *n_dev < n ? *n_dev : n;
+        if ((size_t)blockIdx.x * kSortTile >= n)
+            return;
+    }
+    {
+        extern __shared__ __align__(16) unsigned char smem_raw[];
+        SortSmem &S = *reinterpret_cast<SortSmem *>(smem_raw);
+        if (threadIdx.x == 0)
+            S.tile = atomicAdd(ticket, 1u); // (a skipped pass draws tickets nobody reads)
+        uint4 *z = reinterpret_cast<uint4 *>(&S.wcnt[0][0]);
+        for (int i = threadIdx.x; i < kSortWarps * kRadix / 4; i += kSortThreads)
+            z[i] = make_uint4(0u, 0u, 0u, 0u);
+        __syncthreads();
+    }
+    if (pl.x)
+        return; // every key has the same digit in this pass: nothing moves
+    const unsigned *kin  = reinterpret_cast<const unsigned *>(pl.w == 0 ? B.src_k : (pl.w == 1 ? B.p0 : B.p1));
+    const unsigned *vin  = reinterpret_cast<const unsigned *>(B.src_v);
+    unsigned       *kout = reinterpret_cast<unsigned *>(osel == 3 ? B.dst_k : (osel == 1 ? B.p0 : B.p1));
+    unsigned       *vout = reinterpret_cast<unsigned *>(B.dst_v);
+    if (pl.y == 0 && pl.z != 0)
+        sort_pass_body<false, 4, false, 1, false>(kin, vin, kout, vout, n, shift, flip, nullptr, 0u, gbase, ticket, desc,
+                                                  NoPeer(), n_dev);
+    else if (pl.y != 0 && pl.z != 0)
+        sort_pass_body<false, 4, false, 2, false>(kin, vin, kout, vout, n, shift, flip, nullptr, 0u, gbase, ticket, desc,
+                                                  NoPeer(), n_dev);
+    else if (pl.y != 0)
+        sort_pass_body<false, 4, false, 3, false>(kin, vin, kout, vout, n, shift, flip, nullptr, 0u, gbase, ticket, desc,
+                                                  NoPeer(), n_dev);
+    else
+        sort_pass_body<false, 4, false, 0, false>(kin, vin, kout, vout, n, shift, flip, nullptr, 0u, gbase, ticket, desc,
+                                                  NoPeer(), n_dev);
+}
+
 // ---------------------------------------------------------------------------------------------------
 // Splitters of the multi-GPU sample sort, chosen on the device with no collective call: every rank takes 512
 // regular samples of its keys (in ordered space: key ^ flip), the samples are exchanged through the peer windows
@@ -878,12 +998,14 @@ __global__ void __launch_bounds__(kSplitThreads, 1)
 }
 
 // scratch layout (bytes): [0,16) hist ticket | [16, 16+4 KiB) digit offsets [4][256]
-//                         | [4112, 4128) pass tickets | descriptors [passes][tiles][256] from 4128
-constexpr size_t kSortOffHist = 16, kSortOffTickets = 16 + 4 * kRadix * 4, kSortOffDesc = kSortOffTickets + 16;
+//                         | [4112, 4128) pass tickets | [4128, 4256) pass plan | descriptors [passes][tiles][256] from 4256
+constexpr size_t kSortOffHist = 16, kSortOffTickets = 16 + 4 * kRadix * 4, kSortOffPlan = kSortOffTickets + 16,
+                 kSortOffDesc = kSortOffPlan + 4 * 32; // (+ the pass plan: 4 x 8 words, see SortPlanBufs)
 static_assert(kSortOffDesc % 16 == 0, "descriptor rows are zeroed with 16-byte stores");
 
 static int g_sort_lb = 4; // look-back descriptors fetched per round trip (1, 4 or 8)
 static bool g_sort_peer_bulk = true; // peer partition pass (pair format): cp.async.bulk shared -> peer global
+static bool g_sort_plan = true;  // passes whose digit is the same for every key are skipped (device-side plan)
 static bool g_sort_pairs = true; // intermediate results as (key, value) pairs in library-owned buffers (2 x 8N bytes)
 constexpr size_t kSortPairsMin = 1u << 16;
 
@@ -923,6 +1045,21 @@ static int launch_pass_io(unsigned tiles, cudaStream_t stream, const void *in_a,
     return (int)cudaGetLastError();
 }
 
+// a pass of the planned pipeline: formats and buffers are read from the device-side plan entry
+static int launch_pass_dyn(unsigned tiles, cudaStream_t stream, const unsigned *plan_entry, const SortPlanBufs &bufs,
+                           unsigned n, unsigned shift, unsigned flip, const unsigned *gbase, unsigned *ticket,
+                           unsigned *desc, const unsigned *n_dev)
+{
+    int        st = 0;
+    DeviceCtx *c  = ctx(&st);
+    if (!c)
+        return st;
+    B200_TRY((cudaError_t)opt_in_smem(c, kAttrSortPassDyn, sort_pass_plan_kernel, sizeof(SortSmem)));
+    sort_pass_plan_kernel<<<tiles, kSortThreads, sizeof(SortSmem), stream>>>(plan_entry, bufs, n, shift, flip, gbase, ticket,
+                                                                           desc, n_dev);
+    return (int)cudaGetLastError();
+}
+
 template <bool kBucket, typename... Args> static int launch_pass_lb(Args... args)
 {
     if (g_sort_lb <= 1)
@@ -959,6 +1096,14 @@ static int sort_kv(uint32_t *d_dstKey, uint32_t *d_dstVal, uint32_t *d_bufKey, u
     unsigned *ghist   = reinterpret_cast<unsigned *>(base + kSortOffHist);
     unsigned *tickets = reinterpret_cast<unsigned *>(base + kSortOffTickets);
     const unsigned flip = sortDir ? 0u : 0xffffffffu;
+    unsigned *plan = reinterpret_cast<unsigned *>(base + kSortOffPlan);
+    // planned pipeline (passes with a single digit are skipped, see make_sort_plan): the pair-buffer pipeline only
+    const bool pair_pipeline = d_srcVal == nullptr || (g_sort_pairs && g_sort_lb == 4 && N >= kSortPairsMin);
+    bool       planned       = g_sort_plan && pair_pipeline;
+    if (planned && ensure(c->sort_pairs, 2 * N * sizeof(uint2), stream) != 0) {
+        cudaGetLastError();
+        planned = false;
+    }
 
     {
         B200_TRY((cudaError_t)opt_in_smem(c, kAttrSortHist4, sort_hist4_kernel, 4 * kRadix * 32 * 4));
@@ -968,10 +1113,25 @@ static int sort_kv(uint32_t *d_dstKey, uint32_t *d_dstVal, uint32_t *d_bufKey, u
             grid = 1;
         sort_hist4_kernel<<<grid, kHist4Threads, 4 * kRadix * 32 * 4, stream>>>(
             d_srcKey, N, flip, ghist, hticket, d_n, reinterpret_cast<uint4 *>(base + kSortOffDesc), 4 * desc_bytes / 16,
-            d_srcVal == nullptr);
+            d_srcVal == nullptr, planned ? plan : nullptr);
         B200_TRY(cudaGetLastError());
     }
 
+    if (planned) {
+        SortPlanBufs bufs;
+        bufs.src_k = d_srcKey;
+        bufs.src_v = d_srcVal;
+        bufs.p0    = c->sort_pairs.ptr;
+        bufs.p1    = reinterpret_cast<uint2 *>(c->sort_pairs.ptr) + N;
+        bufs.dst_k = d_dstKey;
+        bufs.dst_v = d_dstVal;
+        for (int p = 0; p < 4; p++)
+            B200_TRY((cudaError_t)launch_pass_dyn(tiles, stream, plan + p * 8, bufs, (unsigned)N, 8u * p, flip,
+                                                  ghist + p * kRadix, tickets + p,
+                                                  reinterpret_cast<unsigned *>(base + kSortOffDesc + p * desc_bytes), d_n));
+        count_launch(5);
+        return 0;
+    }
     if (d_srcVal == nullptr) {
         // the input IS a pair buffer (the receive buffer of the sharded sort): every pass reads pairs
         B200_TRY((cudaError_t)ensure(c->sort_pairs, 2 * N * sizeof(uint2), stream));
@@ -1159,6 +1319,11 @@ extern "C" int b200_tune_sort_peer_bulk(int on)
     g_sort_peer_bulk = on != 0;
     return 0;
 }
+extern "C" int b200_tune_sort_plan(int on)
+{
+    g_sort_plan = on != 0;
+    return 0;
+}
 extern "C" int b200_tune_sort_pairs(int on)
 {
     g_sort_pairs = on != 0;
@@ -1186,6 +1351,7 @@ extern "C" int b200_sort_reserve(size_t N)
     B200_TRY((cudaError_t)opt_in_smem(c, kAttrMisc0, sort_pass_kernel<false, 4, false, 1>, sizeof(SortSmem)));
     B200_TRY((cudaError_t)opt_in_smem(c, kAttrMisc1, sort_pass_kernel<false, 4, false, 2>, sizeof(SortSmem)));
     B200_TRY((cudaError_t)opt_in_smem(c, kAttrMisc2, sort_pass_kernel<false, 4, false, 3>, sizeof(SortSmem)));
+    B200_TRY((cudaError_t)opt_in_smem(c, kAttrSortPassDyn, sort_pass_plan_kernel, sizeof(SortSmem)));
     B200_TRY((cudaError_t)opt_in_smem(c, kAttrSortHist4, sort_hist4_kernel, 4 * kRadix * 32 * 4));
     B200_TRY((cudaError_t)opt_in_smem(c, kAttrSortPass1, sort_pass_kernel<false, 4>, sizeof(SortSmem)));
     return 0;
@@ -1227,6 +1393,7 @@ int sort_preload()
     B200_TRY((cudaError_t)opt_in_smem(c, kAttrMisc0, sort_pass_kernel<false, 4, false, 1>, sizeof(SortSmem)));
     B200_TRY((cudaError_t)opt_in_smem(c, kAttrMisc1, sort_pass_kernel<false, 4, false, 2>, sizeof(SortSmem)));
     B200_TRY((cudaError_t)opt_in_smem(c, kAttrMisc2, sort_pass_kernel<false, 4, false, 3>, sizeof(SortSmem)));
+    B200_TRY((cudaError_t)opt_in_smem(c, kAttrSortPassDyn, sort_pass_plan_kernel, sizeof(SortSmem)));
     return 0;
 }
 } // namespace b200

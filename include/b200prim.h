@@ -94,6 +94,8 @@ int b200_integral_image_u8_async(uint32_t *d_out, const uint8_t *d_img, size_t w
 /* sort: replaces mergeSort() (mergeSort.cu:471-537): STABLE key-value sort, sortDir != 0 ascending,
  * == 0 descending, ties keep source order.  Result in dst, buf is scratch, src is left untouched.
  * Any N >= 0 (the sample asserts N % 1024 == 0 and N <= 2^22).  src may not alias dst/buf.
+ * Four 8-bit LSD passes; a pass whose digit is the same for every key is skipped (decided on the device from the
+ * digit histograms, no host round trip): the sample's own keys, rand() % 65536, cost two passes.
  * d_srcVal == NULL: d_srcKey is an array of N interleaved (key, value) pairs (8 bytes each, 16-byte aligned) -- the
  * format of the sharded sort's receive buffers; buf is then unused and may be NULL. */
 int b200_sort_kv_async(uint32_t *d_dstKey, uint32_t *d_dstVal, uint32_t *d_bufKey, uint32_t *d_bufVal,

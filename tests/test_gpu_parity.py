@@ -789,6 +789,42 @@ def test_sort_with_device_side_count(prim):
             assert bool((dk[n:] == -7).all()), "nothing beyond the counted pairs may be written"
 
 
+@pytest.mark.parametrize("kind", ["mod65536", "mod256", "const", "hi16", "byte1", "byte3", "bytes0+2", "u32"])
+def test_sort_skips_single_digit_passes(prim, kind):
+    """The pass plan made on the device (radix_sort.cu: make_sort_plan): a pass whose digit is the same for every key
+    is not run, the remaining passes are re-chained over the pair buffers.  The sample's own keys (rand() % 65536,
+    mergeSort/main.cpp:48,68) have two such passes.  Stable order bit-exact for every position of the varying bytes,
+    both directions, split and pair-buffer input, host and device-side count, and with the plan switched off."""
+    rng = np.random.default_rng(41)
+    n = (1 << 17) + 8192 + 5  # (the planned pipeline starts at 65536 pairs)
+    r = rng.integers(0, 1 << 32, n, dtype=np.uint64).astype(np.uint32)
+    keys = {"mod65536": r & 0xFFFF, "mod256": r & 0xFF, "const": np.full(n, 0x12345678, np.uint32),
+            "hi16": r & 0xFFFF0000, "byte1": r & 0xFF00, "byte3": r & 0xFF000000, "bytes0+2": r & 0x00FF00FF,
+            "u32": r}[kind].astype(np.uint32)
+    vals = rng.integers(0, 1 << 32, n, dtype=np.uint64).astype(np.uint32)
+    pairs = np.empty(2 * n, np.uint32)
+    pairs[0::2], pairs[1::2] = keys, vals
+    sp = dev(pairs.view(np.int32))
+    try:
+        for plan in (1, 0):
+            prim.lib.b200_tune_sort_plan(plan)
+            for direction in (1, 0):
+                wk, wv = oracle.stable_sort_kv(keys, vals, direction)
+                gk, gv = run_sort(prim, keys, vals, direction)
+                assert (gk == wk).all() and (gv == wv).all(), (kind, plan, direction, "split input")
+                m = n - 4097  # device-side count below the capacity, pair-buffer input
+                dk, dv = (torch.full((n,), -7, dtype=torch.int32, device="cuda") for _ in range(2))
+                d_n = torch.tensor([m, 0], dtype=torch.int32, device="cuda")
+                prim.sort_kv_dyn(dk, dv, None, None, sp, None, n, d_n, direction)
+                wk, wv = oracle.stable_sort_kv(keys[:m], vals[:m], direction)
+                assert (dk[:m].cpu().numpy().view(np.uint32) == wk).all(), (kind, plan, direction, "pairs, dyn count")
+                assert (dv[:m].cpu().numpy().view(np.uint32) == wv).all(), (kind, plan, direction, "pairs, dyn count")
+                assert bool((dk[m:] == -7).all()) and bool((dv[m:] == -7).all())
+    finally:
+        prim.lib.b200_tune_sort_plan(1)
+    assert (sp.cpu().numpy().view(np.uint32) == pairs).all()
+
+
 def test_sort_from_a_pair_buffer(prim):
     """d_srcVal == NULL: the input is an array of interleaved (key, value) pairs -- the format of the sharded sort's
     receive buffers (one 8-byte peer store per pair).  Every pass then reads pairs; the result is the usual split
