@@ -56,6 +56,8 @@ SIGNATURES = {
     "b200_p2p_allgather_async": (ci, [vp, sz, vp, vp]),
     "b200_reduce_partial_exchange_async": (ci, [ci, vp, sz, vp, ctypes.c_uint, ctypes.c_uint, vp, vp, vp, vp]),
     "b200_scan_total_exchange_async": (ci, [vp, vp, sz, vp, vp]),
+    "b200_scan_exclusive_shard_async": (ci, [vp, vp, sz, vp, vp, vp]),
+    "b200_tune_scan_shard_tiled": (ci, [ci]),
     "b200_histogram_fused_allreduce_async": (ci, [vp, vp, vp, sz, vp]),
     "b200_p2p_buffer_create": (ci, [sz, ctypes.POINTER(vp), ctypes.c_char_p]),
     "b200_p2p_buffer_open": (ci, [ctypes.c_char_p, ctypes.POINTER(vp)]),

@@ -272,6 +272,12 @@ def scan_total_exchange(d_carry, d_Src, n, d_work, stream=None):
           "scan_total_exchange")
 
 
+def scan_exclusive_shard(d_Dst, d_Src, n, d_work, d_carry, stream=None):
+    """One shard of a sharded exclusive scan, both steps (tile sums + exchange, then the scan of independent tiles)."""
+    check(lib.b200_scan_exclusive_shard_async(_dptr(d_Dst), _dptr(d_Src), n, _dptr(d_work), _dptr(d_carry),
+                                              _stream(stream)), "scan_exclusive_shard")
+
+
 def histogram_fused_allreduce(d_Histogram256, d_Histogram64, d_Data, byteCount, stream=None):
     """Both histograms of ALL ranks' shards on every rank; the bins are exchanged by the kernel itself."""
     check(lib.b200_histogram_fused_allreduce_async(_dptr(d_Histogram256), _dptr(d_Histogram64), _dptr(d_Data),

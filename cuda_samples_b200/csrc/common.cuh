@@ -49,6 +49,7 @@ struct DeviceCtx {
     Scratch reduce;       // partials + ticket
     Scratch hist;         // accumulators + ticket
     Scratch scan;         // state + tile descriptors
+    Scratch scan_tiles;   // sharded scan: [0] ticket, from byte 16 one u32 per 8192-element tile (sum, then prefix)
     Scratch sort;         // digit histograms + descriptors
     Scratch sort_pairs;   // two (key, value) pair buffers for the intermediate results of the radix passes
     Scratch image;        // integral image: band / block carries

@@ -131,7 +131,10 @@ extern "C" int b200_release_scratch_of(int which)
     B200_TRY(cudaDeviceSynchronize());
     switch (which) {
     case 0: release(c->hist); break;
-    case 1: release(c->scan); break;
+    case 1:
+        release(c->scan);
+        release(c->scan_tiles);
+        break;
     case 2:
         release(c->sort);
         release(c->sort_pairs);
@@ -152,6 +155,7 @@ extern "C" int b200_release_scratch(void)
     release(c->reduce);
     release(c->hist);
     release(c->scan);
+    release(c->scan_tiles);
     release(c->sort);
     release(c->sort_pairs);
     release(c->image);

@@ -1,6 +1,9 @@
 // internal.h -- declarations shared by the translation units of libb200prim.so (not installed).
 #pragma once
 #include <atomic>
+#include <cstdint>
+
+#include <cuda_runtime.h>
 
 #include "../../include/b200prim.h"
 
@@ -10,5 +13,8 @@ extern "C" int b200_release_scratch_of(int which);
 
 namespace b200 {
 extern std::atomic<unsigned long long> g_launches;
+// scan.cu: exclusive scan of one 16-byte aligned array of n % 4 == 0 elements whose 8192-element tiles already know their
+// exclusive prefixes (d_tile_prefix, produced by the kernel in front on the stream; read behind griddepcontrol.wait)
+int scan_tiled(uint32_t *d_dst, const uint32_t *d_src, size_t n, const uint32_t *d_tile_prefix, cudaStream_t stream);
 inline void count_launch(unsigned n = 1) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 } // namespace b200

@@ -413,6 +413,168 @@ extern "C" int b200_tune_scan_total_reverse(int on)
     g_scan_total_reverse = on != 0;
     return 0;
 }
+// ---------------------------------------------------------------------------------------------------------------
+// Sharded long scan as reduce-then-scan over 8192-element tiles (16-byte aligned shards of n % 4 == 0 elements).
+// A rank's carry needs the lower ranks' totals, and a total needs the whole shard: the shard is read twice whatever
+// the scan is.  The chained scan spends its second pass waiting on look-backs (5.4 TB/s); here the FIRST pass leaves
+// one sum per tile behind, its last CTA exchanges the shard total with the peers (NVLink windows, no collective call)
+// and turns the tile sums into exclusive tile prefixes -- carry included -- in place, and the second pass
+// (scan.cu: scan_tiled) is a scan with no dependency between tiles at all: the kernel of the sample's "short"
+// arrays, 6.9 TB/s.  The first pass walks the shard back to front, so the second one finds the shard's head in L2.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int      kTileSumThreads = 256;
+constexpr unsigned kTileSumTile    = 8192; // == the tile of scan_kernel (scan.cu: kScanTile)
+
+__global__ void __launch_bounds__(kTileSumThreads)
+    scan_tile_sums_kernel(const unsigned *__restrict__ src, size_t n, unsigned *__restrict__ tsum, unsigned ntiles,
+                          unsigned *__restrict__ ticket, ReduceExchange ex, bool exchange)
+{
+    __shared__ unsigned           s_part[32];
+    __shared__ unsigned           s_carry;
+    __shared__ bool               s_last;
+    __shared__ unsigned long long s_seq;
+    const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    pdl_launch_dependents(); // the scan behind this kernel may load and scan its first tiles under our tail
+    {
+        const unsigned tile  = ntiles - 1 - blockIdx.x;
+        const size_t   base  = (size_t)tile * kTileSumTile;
+        const size_t   rem   = n - base;
+        const unsigned count = rem < kTileSumTile ? (unsigned)rem : kTileSumTile; // a multiple of 4
+        const uint4   *v     = reinterpret_cast<const uint4 *>(src + base);
+        uint4          r[kTileSumTile / 4 / kTileSumThreads];
+#pragma unroll
+        for (int k = 0; k < (int)(kTileSumTile / 4 / kTileSumThreads); k++) {
+            const unsigned idx = k * kTileSumThreads + tid;
+            r[k]               = (4 * idx < count) ? ld_stream_u4(v + idx) : make_uint4(0, 0, 0, 0);
+        }
+        unsigned s = 0;
+#pragma unroll
+        for (int k = 0; k < (int)(kTileSumTile / 4 / kTileSumThreads); k++)
+            s += (r[k].x + r[k].y) + (r[k].z + r[k].w);
+        s = __reduce_add_sync(0xffffffffu, s);
+        if (lane == 0)
+            s_part[warp] = s;
+        __syncthreads();
+        if (tid == 0) {
+            unsigned t = 0;
+#pragma unroll
+            for (int w = 0; w < kTileSumThreads / 32; w++)
+                t += s_part[w];
+            tsum[tile] = t;
+            __threadfence();
+            s_last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+        }
+        __syncthreads();
+        if (!s_last)
+            return;
+    }
+    // ---- last CTA: shard total -> peers -> carry; tile sums -> exclusive tile prefixes (in place) ----------------
+    __threadfence();
+    const unsigned per = (ntiles + kTileSumThreads - 1) / kTileSumThreads; // a contiguous run of tiles per thread
+    const unsigned b0 = tid * per < ntiles ? tid * per : ntiles, b1 = b0 + per < ntiles ? b0 + per : ntiles;
+    unsigned       local = 0;
+    for (unsigned b = b0; b < b1; b++)
+        local += __ldcg(tsum + b);
+    unsigned inc = local; // inclusive scan of the threads' run totals: lanes, then warps
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const unsigned t = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= (unsigned)d)
+            inc += t;
+    }
+    if (lane == 31)
+        s_part[warp] = inc;
+    __syncthreads();
+    unsigned before = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < kTileSumThreads / 32; w++) {
+        before += (w < (int)warp) ? s_part[w] : 0u;
+        total += s_part[w];
+    }
+    unsigned run = before + inc - local;
+    unsigned carry = 0;
+    if (exchange) {
+        if (tid == 0)
+            ex.slots[ex.index] = (double)total;
+        __syncthreads();
+        const unsigned seq = p2p_exchange(ex.p2p, reinterpret_cast<const unsigned *>(ex.slots), 2 * ex.count, &s_seq);
+        if (tid == 0) {
+            unsigned cin = 0;
+            for (unsigned r = 0; r < ex.p2p.rank; r++)
+                cin += (unsigned)(long long)__hiloint2double((int)p2p_peer_word(ex.p2p, seq, r, 2 * ex.index + 1),
+                                                             (int)p2p_peer_word(ex.p2p, seq, r, 2 * ex.index));
+            s_carry = cin;
+            if (ex.carry)
+                *ex.carry = cin;
+        }
+        __syncthreads();
+        carry = s_carry;
+    }
+    run += carry;
+    for (unsigned b = b0; b < b1; b++) {
+        const unsigned x = __ldcg(tsum + b);
+        tsum[b]          = run;
+        run += x;
+    }
+    if (tid == 0)
+        *ticket = 0; // ready for the next call (stream-ordered)
+}
+
+namespace b200 {
+int scan_shard_preload()
+{
+    cudaFuncAttributes fa;
+    B200_TRY(cudaFuncGetAttributes(&fa, scan_tile_sums_kernel));
+    return 0;
+}
+} // namespace b200
+
+static bool g_scan_shard_tiled = true;
+extern "C" int b200_tune_scan_shard_tiled(int on)
+{
+    g_scan_shard_tiled = on != 0;
+    return 0;
+}
+
+// One shard of a sharded exclusive scan, both steps: d_dst = exclusive scan of d_src seeded with the wrapping sum of
+// the LOWER ranks' shards.  Connected peer windows (b200_p2p_connect / b200_ctx) carry the exchange; with a world of
+// one it is a plain scan.  d_work: >= 2 + world doubles of device memory.  Shards that are not 16-byte aligned or
+// whose length is not a multiple of 4 take the chained scan behind b200_scan_total_exchange_async.
+extern "C" int b200_scan_exclusive_shard_async(uint32_t *d_dst, const uint32_t *d_src, size_t n, double *d_work,
+                                               uint32_t *d_carry, b200_stream_t stream_)
+{
+    cudaStream_t   stream = (cudaStream_t)stream_;
+    const P2PArgs *a      = p2p_args();
+    if (!a || a->world == 0 || !d_work || !d_carry)
+        return (int)cudaErrorInvalidValue;
+    const bool tiled = g_scan_shard_tiled && n >= 4 * (size_t)kTileSumTile && (n & 3) == 0 &&
+                       ((((uintptr_t)d_dst) | ((uintptr_t)d_src)) & 15) == 0 && n / kTileSumTile < 0x7fffffffull;
+    if (!tiled) {
+        B200_TRY((cudaError_t)b200_scan_total_exchange_async(d_carry, d_src, n, d_work, stream_));
+        return n ? b200_scan_exclusive_async(d_dst, d_src, 1, n, d_carry, stream_) : 0;
+    }
+    int        st = 0;
+    DeviceCtx *c  = ctx(&st);
+    if (!c)
+        return st;
+    const unsigned ntiles = (unsigned)((n + kTileSumTile - 1) / kTileSumTile);
+    B200_TRY((cudaError_t)ensure(c->scan_tiles, 16 + 4 * (size_t)ntiles, stream));
+    unsigned *ticket = reinterpret_cast<unsigned *>(c->scan_tiles.ptr);
+    unsigned *tsum   = reinterpret_cast<unsigned *>(reinterpret_cast<char *>(c->scan_tiles.ptr) + 16);
+    ReduceExchange ex;
+    ex.p2p      = *a;
+    ex.slots    = d_work;
+    ex.gathered = d_work + 2;
+    ex.sums     = d_work + 1;
+    ex.carry    = d_carry;
+    ex.index    = 0;
+    ex.count    = 1;
+    scan_tile_sums_kernel<<<ntiles, kTileSumThreads, 0, stream>>>(d_src, n, tsum, ntiles, ticket, ex, true);
+    B200_TRY(cudaGetLastError());
+    count_launch();
+    return scan_tiled(d_dst, d_src, n, tsum, stream);
+}
+
 extern "C" int b200_scan_total_exchange_async(uint32_t *d_carry, const uint32_t *d_src, size_t n, double *d_work,
                                               b200_stream_t stream)
 {

@@ -50,6 +50,8 @@ struct ScanParams {
     unsigned        backoff_ns; // pause between unsuccessful look-back polls
     unsigned        incl;       // 0: exclusive; 0xffffffff: inclusive (every element also receives itself)
     int            *count_out;  // compaction mode of the TMA kernel: number of kept elements
+    const unsigned *tile_prefix; // nullable: exclusive prefix of every tile, produced by the kernel in front (sharded
+                                 // scan, reduce.cu: scan_tile_sums_kernel) -- no look-back, no tickets
 };
 
 __device__ __forceinline__ unsigned long long make_desc(unsigned epoch, unsigned state, unsigned value)
@@ -143,7 +145,7 @@ __global__ void __launch_bounds__(kScanThreads, 3)
 
     const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     // Only arrays spanning several tiles need ordered tickets and the look-back descriptors.
-    const bool chained = kLarge && p.tpa > 1;
+    const bool chained = kLarge && p.tpa > 1 && !p.tile_prefix;
     unsigned   tile = blockIdx.x, epoch = 0;
     if (chained) {
         if (threadIdx.x == 0) {
@@ -264,6 +266,10 @@ __global__ void __launch_bounds__(kScanThreads, 3)
 
     // ---- tile level: decoupled look-back -----------------------------------------------------------
     unsigned prefix = p.carry ? __ldg(p.carry) : 0u;
+    if (kLarge && p.tile_prefix) {
+        pdl_wait(); // the tile is loaded and scanned; its prefix is the first thing needed from the kernel in front
+        prefix = ld_relaxed_u32(p.tile_prefix + tile);
+    }
     if (chained) {
         if (warp == 0) {
             if (tile == first_tile) {
@@ -879,6 +885,7 @@ static int scan_impl(uint32_t *d_dst, const uint32_t *d_src, size_t batch, size_
     p.backoff_ns = (unsigned)g_scan_backoff_ns;
     p.incl       = inclusive ? 0xffffffffu : 0u;
     p.count_out  = nullptr;
+    p.tile_prefix = nullptr;
     bool large;
     if (L >= kScanTile || !is_pow2(L) || L < 4) {
         // tile-aligned arrays (look-back inside an array when it spans several tiles)
@@ -992,6 +999,7 @@ int compact_tma(int32_t *d_dst, int32_t *d_count, const int32_t *d_src, size_t n
     p.backoff_ns = (unsigned)g_scan_backoff_ns;
     p.incl       = 0;
     p.count_out  = d_count;
+    p.tile_prefix = nullptr;
     p.lane_seg   = 32;
     p.rows_seg   = kScanRows;
     p.warps_seg  = kScanWarps;
@@ -1017,6 +1025,47 @@ int compact_tma(int32_t *d_dst, int32_t *d_count, const int32_t *d_src, size_t n
     B200_TRY(cudaGetLastError());
     return 0;
 }
+
+// Second pass of the sharded scan (internal.h): every tile's exclusive prefix is known, tiles are independent.
+namespace b200 {
+int scan_tiled(uint32_t *d_dst, const uint32_t *d_src, size_t n, const uint32_t *d_tile_prefix, cudaStream_t stream)
+{
+    ScanParams p;
+    p.total       = n;
+    p.L           = n;
+    p.carry       = nullptr;
+    p.backoff_ns  = 0;
+    p.incl        = 0;
+    p.count_out   = nullptr;
+    p.tile_prefix = d_tile_prefix;
+    p.lane_seg    = 32;
+    p.rows_seg    = kScanRows;
+    p.warps_seg   = kScanWarps;
+    p.packed      = 0;
+    const size_t tiles = (n + kScanTile - 1) / kScanTile;
+    if (tiles == 0)
+        return 0;
+    if (tiles > 0x7fffffffull)
+        return (int)cudaErrorInvalidValue;
+    p.tpa       = (unsigned)tiles;
+    p.num_tiles = (unsigned)tiles;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim            = dim3((unsigned)tiles);
+    cfg.blockDim           = dim3(kScanThreads);
+    cfg.dynamicSmemBytes   = 0;
+    cfg.stream             = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id                                         = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs                                        = at;
+    cfg.numAttrs                                     = g_scan_pdl ? 1 : 0;
+    unsigned           *no_state = nullptr;
+    unsigned long long *no_desc  = nullptr;
+    B200_TRY(cudaLaunchKernelEx(&cfg, scan_kernel<true>, d_dst, d_src, p, no_state, no_desc));
+    count_launch();
+    return 0;
+}
+} // namespace b200
 
 extern "C" int b200_tune_scan_pdl(int on)
 {
@@ -1051,6 +1100,7 @@ extern "C" int b200_scan_reserve(size_t n)
         return st;
     const size_t tiles = (n + kScanTile - 1) / kScanTile; // (40 KiB tiles need fewer)
     B200_TRY((cudaError_t)ensure(c->scan, 16 + 8 * (tiles + tiles / 32 + 64), 0));
+    B200_TRY((cudaError_t)ensure(c->scan_tiles, 16 + 4 * (tiles + 64), 0)); // tile sums / prefixes of a sharded scan
     return 0;
 }
 

@@ -26,6 +26,7 @@ int reduce_preload();
 int hist_preload();
 int sort_preload();
 int scan_preload();
+int scan_shard_preload();
 } // namespace b200
 
 using namespace b200;
@@ -159,6 +160,7 @@ extern "C" int b200_ctx_create(int ndev, const int *devices, b200_ctx **out)
             B200_TRY((cudaError_t)hist_preload());
             B200_TRY((cudaError_t)sort_preload());
             B200_TRY((cudaError_t)scan_preload());
+            B200_TRY((cudaError_t)scan_shard_preload());
             B200_TRY(cudaDeviceSynchronize());
         }
         B200_TRY(cudaHostAlloc(&c->h_work, ndev * 4 * sizeof(double), cudaHostAllocPortable));
@@ -300,16 +302,12 @@ extern "C" int b200_scan_exclusive_sharded(b200_ctx *c, uint32_t *const *d_dst, 
         B200_TRY(cudaSetDevice(c->dev[i]));
         B200_TRY((cudaError_t)b200_scan_reserve(n[i]));
     }
+    // per device: tile sums + exchange of the shard totals (its last CTA waits for the peers' totals), then the scan of
+    // independent tiles -- both launches of a device are enqueued before the next device's: nothing here blocks the host
     for (int i = 0; i < c->ndev; i++) {
         B200_TRY(cudaSetDevice(c->dev[i]));
-        B200_TRY((cudaError_t)b200_scan_total_exchange_async(meta_carry(c, i), d_src[i], n[i], c->work[i],
-                                                             (b200_stream_t)c->stream[i]));
-    }
-    for (int i = 0; i < c->ndev; i++) {
-        B200_TRY(cudaSetDevice(c->dev[i]));
-        if (n[i])
-            B200_TRY((cudaError_t)b200_scan_exclusive_async(d_dst[i], d_src[i], 1, n[i], meta_carry(c, i),
-                                                            (b200_stream_t)c->stream[i]));
+        B200_TRY((cudaError_t)b200_scan_exclusive_shard_async(d_dst[i], d_src[i], n[i], c->work[i], meta_carry(c, i),
+                                                              (b200_stream_t)c->stream[i]));
     }
     return 0;
 }

@@ -101,6 +101,11 @@ class CudaOps:
     def reduce_partial_exchange(self, x, n, slots, index, count, gathered, sums):
         api.reduce_partial_exchange(x, n, slots, index, count, gathered, sums)
 
+    def scan_shard(self, dst, src, n):
+        carry = torch.empty(1, dtype=torch.int32, device=src.device)
+        work = torch.empty(2 + 16, dtype=torch.float64, device=src.device)
+        api.scan_exclusive_shard(dst, src, n, work, carry)
+
     def scan_total_exchange(self, src, n):
         carry = torch.empty(1, dtype=torch.int32, device=src.device)
         work = torch.empty(2 + 16, dtype=torch.float64, device=src.device)
@@ -259,7 +264,7 @@ def scan_sharded(dst, src, n_local, ops=None, group=None):
         ops.scan_with_carry(dst, src, n_local, None)
         return dst
     if p2p_enabled() and isinstance(ops, CudaOps) and world == _P2P["world"]:
-        ops.scan_with_carry(dst, src, n_local, ops.scan_total_exchange(src, n_local))  # 2 kernels, no collective call
+        ops.scan_shard(dst, src, n_local)  # 2 kernels, no collective call (tile sums + exchange, scan of independent tiles)
         return dst
     total = ops.scan_total(src, n_local)
     totals = torch.empty(world, dtype=torch.int32, device=total.device)

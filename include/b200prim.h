@@ -154,6 +154,13 @@ int b200_reduce_partial_exchange_async(int kind, const void *d_in, size_t n, dou
 /* sharded long scan, step 1: shard total -> peers -> *d_carry; d_work: >= 2 + world doubles of scratch */
 int b200_scan_total_exchange_async(uint32_t *d_carry, const uint32_t *d_src, size_t n, double *d_work,
                                    b200_stream_t stream);
+/* one shard of a sharded exclusive scan, both steps on the stream: d_dst = exclusive scan of d_src seeded with the
+ * wrapping sum of the lower ranks' shards (also left in *d_carry).  16-byte aligned shards of n % 4 == 0 elements run
+ * as reduce-then-scan over 8192-element tiles: pass 1 leaves one sum per tile, exchanges the shard total over the peer
+ * windows and turns the sums into tile prefixes, pass 2 scans independent tiles (no look-back); other shapes take
+ * b200_scan_total_exchange_async + the chained scan.  d_work: >= 2 + world doubles. */
+int b200_scan_exclusive_shard_async(uint32_t *d_dst, const uint32_t *d_src, size_t n, double *d_work,
+                                    uint32_t *d_carry, b200_stream_t stream);
 /* large peer-mapped buffers (cudaMalloc + CUDA IPC): create locally, open the peers' handles */
 int b200_p2p_buffer_create(size_t bytes, void **d_ptr, unsigned char *handle_out /* 64 bytes */);
 int b200_p2p_buffer_open(const unsigned char *handle, void **d_peer);

@@ -897,6 +897,24 @@ def test_peer_window_entry_points_world_1(prim):
         assert int(carry.item()) == 0
         total = int(work[0].item()) & 0xFFFFFFFF
         assert total == int(src.sum(dtype=np.uint64) & 0xFFFFFFFF)
+        # one shard of a sharded scan, both steps: tile sums + exchange + tile prefixes, then independent tiles;
+        # ragged / unaligned / short shards take the chained scan behind the total exchange; in place as well
+        big = rng.integers(0, 1 << 32, (1 << 22) + 8192 * 3 + 4 * 77, dtype=np.uint64).astype(np.uint32)
+        dbig = dev(big.view(np.int32))
+        for tiled in (1, 0):
+            prim.lib.b200_tune_scan_shard_tiled(tiled)
+            for off, n in ((0, big.size), (0, 1 << 20), (0, 8192 * 4), (0, 8192 * 4 + 4), (0, 8192 * 3), (4, 1 << 21),
+                           (1, (1 << 20) + 3), (0, 0), (0, 5)):
+                x = big[off:off + n]
+                out = torch.full((n + 8,), -5, dtype=torch.int32, device="cuda")
+                prim.scan_exclusive_shard(out, dbig[off:off + n], n, work, carry)
+                want = oracle.scan_exclusive(x, 1, n) if n else x
+                assert (out[:n].cpu().numpy().view(np.uint32) == want).all(), (tiled, off, n)
+                assert bool((out[n:] == -5).all()) and int(carry.item()) == 0
+            inplace = dbig[:1 << 21].clone()
+            prim.scan_exclusive_shard(inplace, inplace, 1 << 21, work, carry)
+            assert (inplace.cpu().numpy().view(np.uint32) == oracle.scan_exclusive(big[:1 << 21], 1, 1 << 21)).all()
+        prim.lib.b200_tune_scan_shard_tiled(1)
         torch.cuda.synchronize()
         assert prim.p2p_errors() == 0
     finally:
