@@ -340,9 +340,33 @@ def primitives_table(torch, dist, prim, mg, rank, world, peak, barrier, p2p=Fals
 
     def step_scan():
         mg.scan_sharded(dst, src, n)
+    second_pass = None
+    if world > 1 and p2p:
+        # Trial of the tile-prefix path under the timing loop's own conditions (calls back to back, no host sync between
+        # them) with a SHORT peer timeout: a rank that ran ahead of its peers' reads would show up here as lost words
+        # within a second instead of stalling the timed loop for the default 30 s per call.  On any loss every rank
+        # switches to the chained second pass (the path of the earlier records) on fresh windows.
+        from cuda_samples_b200 import api
+        second_pass = "independent tiles seeded with tile prefixes (first pass: tile sums + exchange of the shard totals)"
+        step_scan()  # first call: scratch is sized here, under the default timeout
+        torch.cuda.synchronize()
+        barrier()
+        api.p2p_set_timeout_ms(250)
+        for _ in range(8):
+            step_scan()
+        torch.cuda.synchronize()
+        lost = torch.tensor([int(prim.p2p_errors())], dtype=torch.int64, device="cuda")
+        dist.all_reduce(lost)
+        api.p2p_set_timeout_ms(30000)
+        if int(lost.item()):
+            prim.lib.b200_tune_scan_shard_tiled(0)
+            mg.disable_p2p()  # (the loss count of a window set is sticky: new windows)
+            mg.enable_p2p()
+            second_pass = "chained scan seeded with the carry (the tile-prefix path lost %d words in its trial)" % int(lost.item())
     record("scanExclusiveLarge_2^28", time_steps(torch, step_scan, 20, 4, barrier) / 20, 8 * N_ELEMS,
            {"scaling": "strong", "collective": (("in-kernel NVLink peer-window exchange of shard totals" if p2p else
-                                                "all_gather(G x u32)") if world > 1 else None)})
+                                                "all_gather(G x u32)") if world > 1 else None),
+            "second_pass": second_pass})
     if world == 1:
         def step_scan_short():
             prim.scanExclusiveShort(dst, src, n // 1024, 1024)

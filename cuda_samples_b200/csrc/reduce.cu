@@ -430,6 +430,7 @@ __global__ void __launch_bounds__(kTileSumThreads)
                           unsigned *__restrict__ ticket, ReduceExchange ex, bool exchange)
 {
     __shared__ unsigned           s_part[32];
+    __shared__ unsigned           s_tot[kP2PMaxRanks]; // every rank's shard total of this exchange
     __shared__ unsigned           s_carry;
     __shared__ bool               s_last;
     __shared__ unsigned long long s_seq;
@@ -498,11 +499,18 @@ __global__ void __launch_bounds__(kTileSumThreads)
             ex.slots[ex.index] = (double)total;
         __syncthreads();
         const unsigned seq = p2p_exchange(ex.p2p, reinterpret_cast<const unsigned *>(ex.slots), 2 * ex.count, &s_seq);
+        // EVERY rank waits for EVERY rank's total, although only the lower ones enter its carry: that wait is what
+        // keeps the ranks in step.  The windows' slot-reuse rule (p2p.cuh) holds because no rank can start exchange
+        // s + 2 before all ranks have published s + 1; a rank that read nobody's words (rank 0 needs none) would run
+        // ahead through back-to-back calls and overwrite words its peers have not read yet.
+        if (tid < ex.p2p.world)
+            s_tot[tid] = (unsigned)(long long)__hiloint2double((int)p2p_peer_word(ex.p2p, seq, tid, 2 * ex.index + 1),
+                                                               (int)p2p_peer_word(ex.p2p, seq, tid, 2 * ex.index));
+        __syncthreads();
         if (tid == 0) {
             unsigned cin = 0;
             for (unsigned r = 0; r < ex.p2p.rank; r++)
-                cin += (unsigned)(long long)__hiloint2double((int)p2p_peer_word(ex.p2p, seq, r, 2 * ex.index + 1),
-                                                             (int)p2p_peer_word(ex.p2p, seq, r, 2 * ex.index));
+                cin += s_tot[r];
             s_carry = cin;
             if (ex.carry)
                 *ex.carry = cin;
