@@ -6,6 +6,7 @@ Every rank regenerates the global input with the counter-based generator on the 
 its own slice of the result against the oracle run on the whole input."""
 import os
 import sys
+import time
 
 import numpy as np
 import torch
@@ -72,6 +73,32 @@ def main():
         small_exchanges("p2p:")
     torch.cuda.synchronize()
     check("p2p_errors", prim.p2p_errors() == 0)
+    # Back to back with no host sync between the calls and the ranks deliberately out of step: every exchange must
+    # make every rank wait for every rank, or a rank that needs nobody's words (rank 0 of a scan) runs ahead and
+    # overwrites window slots its peers have not read yet (seen on 8 GPUs as lost words, never as wrong results).
+    n = 1 << 24
+    src = torch.empty(n, dtype=torch.int32, device="cuda")
+    prim.generate(src, "u31", rank * n, n, 2009)
+    dst = torch.empty_like(src)
+    want = oracle.scan_exclusive(oracle.generate("u31", 0, world * n, 2009), 1, world * n)[rank * n:(rank + 1) * n]
+    xi = torch.empty(n, dtype=torch.int32, device="cuda")
+    prim.generate(xi, "i32_byte", rank * n, n, 1)
+    want_sum = oracle.reduce(oracle.generate("i32_byte", 0, world * n, 1))
+    prim.p2p_set_timeout_ms(2000)
+    for late in range(min(world, 3)):
+        torch.cuda.synchronize()
+        dist.barrier()
+        if rank == late:
+            time.sleep(0.05)
+        for _ in range(40):
+            mg.scan_sharded(dst, src, n)
+            gi = mg.reduce_sharded(xi, n)
+        torch.cuda.synchronize()
+        check("p2p back-to-back scan (rank %d late)" % late, (dst.cpu().numpy().view(np.uint32) == want).all())
+        check("p2p back-to-back reduce (rank %d late)" % late, int(gi.item()) == want_sum)
+        check("p2p back-to-back errors (rank %d late)" % late, prim.p2p_errors() == 0)
+    prim.p2p_set_timeout_ms(30000)
+    del src, dst, xi
     # latency of the exchange alone: NCCL all_gather vs the peer-window kernel (CUDA events, 200 calls each)
     small = torch.zeros(2, dtype=torch.float64, device="cuda")
     out = torch.empty(2 * world, dtype=torch.float64, device="cuda")
