@@ -352,21 +352,32 @@ def primitives_table(torch, dist, prim, mg, rank, world, peak, barrier, p2p=Fals
         torch.cuda.synchronize()
         barrier()
         api.p2p_set_timeout_ms(250)
-        for _ in range(8):
+        for _ in range(24):  # as many calls as the timed region below issues
             step_scan()
         torch.cuda.synchronize()
         lost = torch.tensor([int(prim.p2p_errors())], dtype=torch.int64, device="cuda")
         dist.all_reduce(lost)
-        api.p2p_set_timeout_ms(30000)
         if int(lost.item()):
+            api.p2p_set_timeout_ms(30000)
             prim.lib.b200_tune_scan_shard_tiled(0)
             mg.disable_p2p()  # (the loss count of a window set is sticky: new windows)
             mg.enable_p2p()
             second_pass = "chained scan seeded with the carry (the tile-prefix path lost %d words in its trial)" % int(lost.item())
-    record("scanExclusiveLarge_2^28", time_steps(torch, step_scan, 20, 4, barrier) / 20, 8 * N_ELEMS,
-           {"scaling": "strong", "collective": (("in-kernel NVLink peer-window exchange of shard totals" if p2p else
-                                                "all_gather(G x u32)") if world > 1 else None),
-            "second_pass": second_pass})
+    t_scan = time_steps(torch, step_scan, 20, 4, barrier) / 20
+    scan_extra = {"scaling": "strong", "collective": (("in-kernel NVLink peer-window exchange of shard totals" if p2p else
+                                                       "all_gather(G x u32)") if world > 1 else None),
+                  "second_pass": second_pass}
+    if world > 1 and p2p:
+        torch.cuda.synchronize()
+        lost = torch.tensor([int(prim.p2p_errors())], dtype=torch.int64, device="cuda")
+        dist.all_reduce(lost)
+        api.p2p_set_timeout_ms(30000)
+        scan_extra["lost_words_in_timed_loop"] = int(lost.item())  # 0, or the row below is void
+        if int(lost.item()):  # (all-reduced: every rank takes this branch together) fresh windows for the sort rows
+            prim.lib.b200_tune_scan_shard_tiled(0)
+            mg.disable_p2p()
+            mg.enable_p2p()
+    record("scanExclusiveLarge_2^28", t_scan, 8 * N_ELEMS, scan_extra)
     if world == 1:
         def step_scan_short():
             prim.scanExclusiveShort(dst, src, n // 1024, 1024)
