@@ -32,6 +32,7 @@ SIGNATURES = {
     "b200_scalar_prod_async": (ci, [vp, vp, vp, ci, ci, vp]),
     "b200_scan_exclusive_async": (ci, [vp, vp, sz, sz, vp, vp]),
     "b200_scan_total_async": (ci, [vp, vp, sz, vp]),
+    "b200_scan_exclusive_noalloc_async": (ci, [vp, vp, sz, sz, vp, vp]),
     "b200_scan_inclusive_async": (ci, [vp, vp, sz, sz, vp, vp]),
     "b200_compact_positive_async": (ci, [vp, vp, vp, sz, vp]),
     "b200_integral_image_u8_async": (ci, [vp, vp, sz, sz, vp]),

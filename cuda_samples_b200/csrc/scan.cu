@@ -20,6 +20,9 @@
 #include "common.cuh"
 #include "internal.h"
 
+#include <cstdio>
+#include <mutex>
+
 #ifndef B200_SCAN_LOAD_EVICT_FIRST
 #define B200_SCAN_LOAD_EVICT_FIRST 0
 #endif
@@ -1101,6 +1104,125 @@ extern "C" int b200_scan_reserve(size_t n)
     const size_t tiles = (n + kScanTile - 1) / kScanTile; // (40 KiB tiles need fewer)
     B200_TRY((cudaError_t)ensure(c->scan, 16 + 8 * (tiles + tiles / 32 + 64), 0));
     B200_TRY((cudaError_t)ensure(c->scan_tiles, 16 + 4 * (tiles + 64), 0)); // tile sums / prefixes of a sharded scan
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Scan for callers that must not allocate.
+//
+// Some users of this library are not free to call cudaMalloc: a plug-in inside a host application that handed the
+// whole device to its own memory pool at start-up (a later cudaMalloc fails or steals from the pool), a service
+// running under a fixed memory budget that is audited once and then frozen, a real-time loop in which the implicit
+// device-wide synchronisation of cudaMalloc / cudaFree would stall every other stream.  The other scan entry points
+// keep their tile descriptors in grow-on-demand cudaMalloc'ed scratch (context.cu: ensure), so such a caller could
+// not use them the first time, or the first time with a longer array.  This one keeps the descriptors in a fixed
+// array that is part of the library image instead: loading the library on a device costs that device
+// sizeof(g_scan_noalloc) bytes (about 64 KiB) until the process exits, and nothing is ever allocated or freed here.
+//
+// The price is a size limit (kNoAllocMaxTiles tiles of 8192 elements per call) and ONE array per device shared by every
+// call: see the comment on the entry point.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr unsigned kNoAllocMaxTiles = 8192; // == B200_SCAN_NOALLOC_MAX_TILES (b200prim.h): one array of up to 2^26 elements
+// [0] {epoch | ticket} of scan_kernel, [1] unused (keeps the descriptors 16-byte aligned like the cudaMalloc'ed
+// layout), [2 ..) one 64-bit look-back descriptor per tile.  Zero at load time == epoch 0, no ticket drawn, nothing
+// published: exactly what a freshly zero-filled scratch block is for the other entry points.
+static __device__ __align__(256) unsigned long long g_scan_noalloc[2 + kNoAllocMaxTiles];
+
+// In host code `g_scan_noalloc` is only a handle the runtime knows the array by, NOT its device address: the address
+// is looked up once per device (with that device current) and remembered here.
+static std::mutex          g_noalloc_mutex;
+static unsigned long long *g_noalloc_addr[64] = {};
+
+static int noalloc_scratch(unsigned long long **out)
+{
+    int dev = -1;
+    B200_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64)
+        return (int)cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_addr[dev]) {
+        void *p = nullptr;
+        B200_TRY(cudaGetSymbolAddress(&p, g_scan_noalloc)); // this device's copy of the array
+        if (!p)
+            return (int)cudaErrorInvalidSymbol;
+        g_noalloc_addr[dev] = static_cast<unsigned long long *>(p);
+    }
+    *out = g_noalloc_addr[dev];
+    return 0;
+}
+
+// Same result as b200_scan_exclusive_async (batchSize independent exclusive +scans of arrayLength u32, wrapping,
+// optional d_carry seed, in place allowed), computed by the register-staged chained-scan kernel with its descriptors
+// in the library's built-in array.  Makes no allocation of any kind, on any call.
+//   * Limit: the launch may need at most 8192 tiles of 8192 elements -- batchSize * ceil(arrayLength / 8192) for
+//     arrays of 8192 elements or more and for lengths that are not a power of two, ceil(batchSize * arrayLength /
+//     8192) for shorter power-of-two lengths.  One array can be 2^26 elements (256 MiB) long.  Anything larger is
+//     refused with cudaErrorInvalidValue and a line on stderr that names the limit; nothing is launched.
+//   * The first call on each device looks the array's address up (cudaGetSymbolAddress, which may also make the
+//     runtime load the library's device code).  Make that first call outside any stream capture.
+//   * All calls on a device use the same array and find in it what the previous call left.  Nothing has to be
+//     cleared by the caller: the one word that must be zero when a launch starts, the ticket counter, is put back to
+//     zero by the kernel itself (the CTA that draws the last ticket re-arms it and advances the epoch that tags the
+//     descriptors, so stale descriptors are never mistaken for fresh ones).  That only works when the calls do not
+//     overlap on the GPU: two of them running at once -- different streams with no event between them -- draw from the
+//     same ticket counter and overwrite each other's descriptors, which gives wrong results or a hang.  Keep them on one
+//     stream or order them with events.
+extern "C" int b200_scan_exclusive_noalloc_async(uint32_t *d_dst, const uint32_t *d_src, size_t batch, size_t L,
+                                                 const uint32_t *d_carry, b200_stream_t stream_)
+{
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (batch == 0 || L == 0)
+        return 0;
+    int st = 0;
+    if (!ctx(&st)) // sm_100a check only; the context object holds no memory that this path uses
+        return st;
+    ScanParams p;
+    p.total       = batch * L;
+    p.L           = L;
+    p.carry       = d_carry;
+    p.backoff_ns  = 0;
+    p.incl        = 0;
+    p.count_out   = nullptr;
+    p.tile_prefix = nullptr;
+    const bool large = L >= kScanTile || !is_pow2(L) || L < 4;
+    size_t     tiles;
+    if (large) {
+        const size_t tpa = (L + kScanTile - 1) / kScanTile;
+        // (no overflow: tpa <= 8192 in the product, batch < 2^32 is checked below)
+        tiles = (tpa > kNoAllocMaxTiles || batch > 0xffffffffull) ? (size_t)kNoAllocMaxTiles + 1 : tpa * batch;
+        p.tpa = (unsigned)(tpa > kNoAllocMaxTiles ? 0 : tpa);
+        p.lane_seg       = 32;
+        p.rows_seg       = kScanRows;
+        p.warps_seg      = kScanWarps;
+        p.packed         = 0;
+    }
+    else {
+        tiles       = (p.total + kScanTile - 1) / kScanTile;
+        p.tpa       = 1;
+        p.lane_seg  = (unsigned)(L / 4 < 32 ? L / 4 : 32);
+        p.rows_seg  = (unsigned)(L / 128 < 1 ? 1 : (L / 128 > kScanRows ? kScanRows : L / 128));
+        p.warps_seg = (unsigned)(L / 512 < 1 ? 1 : L / 512);
+        p.packed    = 1;
+    }
+    if (tiles > kNoAllocMaxTiles || batch > 0xffffffffull) {
+        fprintf(stderr,
+                "b200_scan_exclusive_noalloc_async: %zu arrays of %zu elements need more than the %u tiles of 8192 "
+                "elements that the built-in scratch holds (one array: at most %zu elements); use "
+                "b200_scan_exclusive_async, which allocates\n",
+                batch, L, kNoAllocMaxTiles, (size_t)kNoAllocMaxTiles * kScanTile);
+        return (int)cudaErrorInvalidValue;
+    }
+    p.num_tiles = (unsigned)tiles;
+    unsigned long long *scratch = nullptr;
+    B200_TRY((cudaError_t)noalloc_scratch(&scratch));
+    unsigned           *state = reinterpret_cast<unsigned *>(scratch);
+    unsigned long long *desc  = scratch + 2;
+    if (large)
+        scan_kernel<true><<<p.num_tiles, kScanThreads, 0, stream>>>(d_dst, d_src, p, state, desc);
+    else
+        scan_kernel<false><<<p.num_tiles, kScanThreads, 0, stream>>>(d_dst, d_src, p, state, desc);
+    count_launch();
+    B200_TRY(cudaGetLastError());
     return 0;
 }
 

@@ -121,6 +121,26 @@ int b200_segmented_sort_kv_async(uint32_t *d_dstKey, uint32_t *d_dstVal, const u
 int b200_scan_reserve(size_t n);
 int b200_sort_reserve(size_t N);
 
+/* Scan for callers that cannot allocate device memory -- NO COUNTERPART IN THE REFERENCE (the samples cudaMalloc their
+ * scratch in initScan, scan.cu:182-186); added for users of this library, not to mirror a sample.
+ * Who needs it: a plug-in whose host application gave the whole GPU to its own memory pool at start-up, a service
+ * whose device-memory budget is fixed and audited once, a latency-critical loop that cannot afford the device-wide
+ * synchronisation hidden in cudaMalloc / cudaFree.  b200_scan_exclusive_async grows its tile descriptors with
+ * cudaMalloc on first use and whenever a longer array arrives; this entry point never allocates or frees anything.
+ * Its descriptors live in a fixed array inside the library image: about 64 KiB of every GPU that loads
+ * libb200prim.so, held until the process exits.
+ * Same arguments and same result as b200_scan_exclusive_async.  Limit: the call may span at most
+ * B200_SCAN_NOALLOC_MAX_TILES tiles of 8192 elements -- batchSize * ceil(arrayLength / 8192) tiles (power-of-two
+ * lengths below 8192 are packed: ceil(batchSize * arrayLength / 8192)) -- so one array can be up to 2^26 elements;
+ * larger requests return cudaErrorInvalidValue (1), print the limit on stderr and launch nothing.
+ * The first call on each device also looks up the array's device address; make it before any stream capture.
+ * Every call on a device shares the one array and inherits what the previous call left in it; the kernel itself
+ * resets the only word that has to start at zero, so callers clear nothing -- but two calls that can run on the GPU
+ * at the same time (different streams, no event between them) corrupt each other.  Keep them stream-ordered. */
+#define B200_SCAN_NOALLOC_MAX_TILES 8192
+int b200_scan_exclusive_noalloc_async(uint32_t *d_dst, const uint32_t *d_src, size_t batchSize, size_t arrayLength,
+                                      const uint32_t *d_carry, b200_stream_t stream);
+
 /* counter-based synthetic data, bit-identical to oracle_generate() (oracle/oracle.c): element i of
  * the stream depends only on (seed, first + i, kind, param), so shards are filled in place. */
 int b200_generate_async(void *d_out, size_t first, size_t n, uint64_t seed, int kind, uint32_t param,
