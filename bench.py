@@ -29,6 +29,7 @@ if ROOT not in sys.path:
 
 METRIC = "HBM GB/s (% of B200 peak) per primitive; sort Gkeys/s at 1/2/4/8 GPUs"
 N_ELEMS = 1 << 28
+HIST_BYTES_PER_RANK = 4 << 30  # configs[3]: 32 GiB over 8 GPUs; timed AND checked against the gold at this size
 WORKLOAD = "reduce<int> + reduce<float> SUM over 2^28 elements each per GPU (BASELINE configs[1])"
 OVERLAP = os.environ.get("B200_BENCH_OVERLAP", "0") == "1"  # async all_gather behind the next step's kernels
 HBM_NOMINAL = 8000.0
@@ -316,7 +317,7 @@ def primitives_table(torch, dist, prim, mg, rank, world, peak, barrier, p2p=Fals
     torch.cuda.current_stream().wait_stream(side)
     del bufs
     # --- histogram, 4 GiB per GPU, both histograms in one pass (BASELINE configs[3] shape: 32 GiB over 8)
-    big = 4 << 30
+    big = HIST_BYTES_PER_RANK
     d = torch.empty(big, dtype=torch.uint8, device="cuda")
     prim.generate(d, "bytes", rank * big, big, 2009)
 
@@ -454,8 +455,8 @@ def primitives_table(torch, dist, prim, mg, rank, world, peak, barrier, p2p=Fals
         "frac_of_measured_peak": round(68 * N_ELEMS / t / 1e9 / (peak * world), 4),
         "frac_of_nominal_8TBs": round(68 * N_ELEMS / t / 1e9 / (HBM_NOMINAL * world), 4),
         "scaling": "strong", "dataset": "D1 unique keys, val=i, ascending",
-        "collective": (("sample sort: all_gather of samples (NCCL) + partition pass storing into the peers' receive "
-                        "buffers over NVLink (no all-to-all call)") if p2p else
+        "collective": (("sample sort, no NCCL call: samples exchanged through the NVLink peer windows by the splitter "
+                        "kernel, partition pass storing into the peers' receive buffers over NVLink") if p2p else
                        "sample sort: all_gather + all_to_all") if world > 1 else None}
     if world > 1 and p2p:
         # ---- exchange phase alone, against the NVLink roofline (north_star: "NVLink roofline for the exchange phases")
@@ -584,21 +585,31 @@ def parity_block(torch, dist, prim, mg, oracle, rank, world, xi, xf, gpu_sums, e
             fails.append(k)
     del hi, hf
 
-    # ---- histogram64 + histogram256 sharded, 1 GiB per rank: bins bit-exact vs histogram256CPU/64CPU summed (u32)
-    nb = 1 << 30
+    # ---- histogram64 + histogram256 sharded at the TIMED size, 4 GiB per rank (32 GiB over 8 GPUs = configs[3]):
+    #      bins bit-exact vs histogram256CPU/64CPU, whose byteCount is a uint (histogram_gold.cpp:32,49), so the gold
+    #      runs over 1 GiB chunks and the u32 bins are added up
+    nb = HIST_BYTES_PER_RANK
     d = torch.empty(nb, dtype=torch.uint8, device="cuda")
     prim.generate(d, "bytes", rank * nb, nb, 2009)
     h256, h64 = mg.histogram_sharded(d, nb)
-    hd = d.cpu().numpy()
-    want256 = allsum_i64(gold.histogram256(hd).astype(np.int64)) & 0xFFFFFFFF
-    want64 = allsum_i64(gold.histogram64(hd).astype(np.int64)) & 0xFFFFFFFF
+    g256, g64 = np.zeros(256, np.int64), np.zeros(64, np.int64)
+    t0 = time.perf_counter()
+    for c0 in range(0, nb, 1 << 30):
+        hd = d[c0:c0 + (1 << 30)].cpu().numpy()
+        g256 += gold.histogram256(hd).astype(np.int64)
+        g64 += gold.histogram64(hd).astype(np.int64)
+        del hd
+    out["gold_histogram_seconds"] = time.perf_counter() - t0
+    want256 = allsum_i64(g256) & 0xFFFFFFFF
+    want64 = allsum_i64(g64) & 0xFFFFFFFF
     out["histogram256_bit_exact"] = bool((h256.cpu().numpy().view(np.uint32) == want256).all())
     out["histogram64_bit_exact"] = bool((h64.cpu().numpy().view(np.uint32) == want64).all())
-    out["histogram_sizes"] = "1 GiB per rank (the timed run uses 4 GiB per rank; same kernel, same exchange)"
+    out["histogram_sizes"] = "%d GiB per rank, %d GiB in all: the size the histogram row times" % (nb >> 30,
+                                                                                                  (nb >> 30) * world)
     for k in ("histogram256_bit_exact", "histogram64_bit_exact"):
         if not out[k]:
             fails.append(k)
-    del d, hd
+    del d
 
     # ---- scanExclusiveLarge, the FULL 2^28-element array split into contiguous shards: element-wise bit-exact
     n = N_ELEMS // world
@@ -819,6 +830,8 @@ def run_ours(args):
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
+        if parity.get("all_ok") is not True:  # `failures` is all-reduced: every rank knows, every rank says so
+            sys.exit(3)
         return
 
     # ---- CPU baseline on rank 0 (N=1 only): the gold path, single thread as shipped, whole workload once
@@ -869,9 +882,44 @@ def run_ours(args):
                     "pcie_gbs_sum_of_per_rank_bests": pcie_sum_of_bests,
                     "host_buffer": host_info},
             "gpu_launches": int(launches), "parity": parity, "notes": notes, "primitives": table}
+    # The verdict in a key the driver keeps, and in the exit code (the samples' own drivers return their gold compare
+    # as the process status: histogram/main.cpp:221-227, scan/main.cpp:181, mergeSort/main.cpp:100-118).
+    problems = list(parity.get("failures_this_rank", [])) if parity.get("all_ok") is not True else []
+    if parity.get("all_ok") is not True and not problems:
+        problems.append(parity.get("error", "parity failed on another rank"))
+    for name, row in (table or {}).items() if isinstance(table, dict) else ():
+        if isinstance(row, dict) and row.get("lost_words_in_timed_loop"):
+            problems.append("%s: lost_words_in_timed_loop=%s" % (name, row["lost_words_in_timed_loop"]))
+    if isinstance(table, dict) and "error" in table:
+        problems.append("primitives table: " + str(table["error"]))
+    line["roofline"]["parity_ok"] = not problems
+    line["roofline"]["parity_failures"] = problems
+    line["roofline"]["parity_checked"] = "every primitive vs the samples' CPU gold inside this run, on all %d rank(s)" \
+                                         " (see `parity`)" % world
+    weakest = weakest_primitive(table)
+    if weakest:
+        line["roofline"]["weakest_primitive"] = weakest
     emit(line)
     if world > 1:
         dist.destroy_process_group()
+    if problems:
+        sys.exit(3)
+
+
+NORTH_STAR_ROWS = ("histogram256_64MiB", "histogram64_64MiB", "histogram64+256_fused_4GiB_per_gpu",
+                   "scanExclusiveLarge_2^28", "scanExclusiveShort_L1024_2^28", "mergeSort_kv_2^28")
+
+
+def weakest_primitive(table):
+    """The north-star primitive furthest below its HBM roofline in this run (the headline `roofline` describes the
+    reduce, the easiest kernel of the path)."""
+    worst = None
+    for name in NORTH_STAR_ROWS:
+        row = table.get(name) if isinstance(table, dict) else None
+        frac = row.get("frac_of_measured_peak") if isinstance(row, dict) else None
+        if isinstance(frac, (int, float)) and (worst is None or frac < worst["frac"]):
+            worst = {"name": name, "frac": frac, "n_gpus": row.get("n_gpus")}
+    return worst
 
 
 _REAL_STDOUT = None

@@ -24,6 +24,7 @@ def main():
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     failures = []
+    sort_gold = {}
 
     def check(name, ok):
         if not ok:
@@ -76,6 +77,8 @@ def main():
     # Back to back with no host sync between the calls and the ranks deliberately out of step: every exchange must
     # make every rank wait for every rank, or a rank that needs nobody's words (rank 0 of a scan) runs ahead and
     # overwrites window slots its peers have not read yet (seen on 8 GPUs as lost words, never as wrong results).
+    # All four sharded primitives alternate (histogram -> scan -> reduce -> sort), so every kind of exchange follows
+    # every other kind through the same window slots.
     n = 1 << 24
     src = torch.empty(n, dtype=torch.int32, device="cuda")
     prim.generate(src, "u31", rank * n, n, 2009)
@@ -84,19 +87,45 @@ def main():
     xi = torch.empty(n, dtype=torch.int32, device="cuda")
     prim.generate(xi, "i32_byte", rank * n, n, 1)
     want_sum = oracle.reduce(oracle.generate("i32_byte", 0, world * n, 1))
+    nb = 16 << 20
+    hb = torch.empty(nb, dtype=torch.uint8, device="cuda")
+    prim.generate(hb, "bytes", rank * nb, nb, 2009)
+    whole = oracle.generate("bytes", 0, world * nb, 2009)
+    want_h256, want_h64 = oracle.histogram256(whole), oracle.histogram64(whole)
+    del whole
+    ns = 1 << 22
+    skeys = oracle.generate("key_unique", 0, world * ns, 7, 0)
+    svals = np.arange(world * ns, dtype=np.uint32)
+    sk = torch.from_numpy(skeys[rank * ns:(rank + 1) * ns].view(np.int32).copy()).cuda()
+    sv = torch.from_numpy(svals[rank * ns:(rank + 1) * ns].view(np.int32).copy()).cuda()
+    want_sk, want_sv = oracle.stable_sort_kv(skeys, svals, 1)
+    sort_gold[("key_unique", 0, 1)] = (want_sk, want_sv)
+    mg.sort_sharded(sk, sv, ns, 1)  # first call sizes the receive buffers (it synchronises); the loop below does not
     prim.p2p_set_timeout_ms(2000)
     for late in range(min(world, 3)):
         torch.cuda.synchronize()
         dist.barrier()
         if rank == late:
             time.sleep(0.05)
-        for _ in range(40):
+        for _ in range(24):
+            h256, h64 = mg.histogram_sharded(hb, nb)
             mg.scan_sharded(dst, src, n)
             gi = mg.reduce_sharded(xi, n)
+            dk, dv, meta, _ = mg.sort_sharded(sk, sv, ns, 1, sync=False)
         torch.cuda.synchronize()
-        check("p2p back-to-back scan (rank %d late)" % late, (dst.cpu().numpy().view(np.uint32) == want).all())
-        check("p2p back-to-back reduce (rank %d late)" % late, int(gi.item()) == want_sum)
-        check("p2p back-to-back errors (rank %d late)" % late, prim.p2p_errors() == 0)
+        tag = " (rank %d late)" % late
+        check("p2p back-to-back hist" + tag, (h256.cpu().numpy().view(np.uint32) == want_h256).all() and
+              (h64.cpu().numpy().view(np.uint32) == want_h64).all())
+        check("p2p back-to-back scan" + tag, (dst.cpu().numpy().view(np.uint32) == want).all())
+        check("p2p back-to-back reduce" + tag, int(gi.item()) == want_sum)
+        host = meta.cpu().numpy().view(np.uint32)
+        m = host[:world * world].reshape(world, world)
+        n_out, off = int(host[-2]), int(m[:, :rank].sum())
+        check("p2p back-to-back sort" + tag, int(host[-1]) == 0 and int(m.sum()) == world * ns and
+              (dk[:n_out].cpu().numpy().view(np.uint32) == want_sk[off:off + n_out]).all() and
+              (dv[:n_out].cpu().numpy().view(np.uint32) == want_sv[off:off + n_out]).all())
+        check("p2p back-to-back errors" + tag, prim.p2p_errors() == 0)
+    del hb, sk, sv, skeys, svals
     prim.p2p_set_timeout_ms(30000)
     del src, dst, xi
     # latency of the exchange alone: NCCL all_gather vs the peer-window kernel (CUDA events, 200 calls each)
@@ -130,7 +159,9 @@ def main():
                 sk = torch.from_numpy(keys[rank * n:(rank + 1) * n].view(np.int32).copy()).cuda()
                 sv = torch.from_numpy(vals[rank * n:(rank + 1) * n].view(np.int32).copy()).cuda()
                 dk, dv, n_out, m = mg.sort_sharded(sk, sv, n, direction, **kw)
-                wk, wv = oracle.stable_sort_kv(keys, vals, direction)
+                if (kind, param, direction) not in sort_gold:
+                    sort_gold[(kind, param, direction)] = oracle.stable_sort_kv(keys, vals, direction)
+                wk, wv = sort_gold[(kind, param, direction)]
                 off = int(m[:, :rank].sum())  # rows = source, cols = destination: everything sent to lower ranks
                 gk, gv = dk[:n_out].cpu().numpy().view(np.uint32), dv[:n_out].cpu().numpy().view(np.uint32)
                 check("%s sort %s dir=%d" % (tag, kind, direction), int(m.sum()) == world * n and
