@@ -76,6 +76,36 @@ int ensure(Scratch &s, size_t bytes, cudaStream_t stream, bool *fresh)
     return 0;
 }
 
+struct PdlNotes {
+    uintptr_t lo[8] = {}, hi[8] = {};
+    unsigned  next = 0;
+};
+static PdlNotes g_pdl_notes[kMaxDevices];
+
+void pdl_note_output(int device, const void *p, size_t bytes)
+{
+    if (!p || !bytes || device < 0 || device >= kMaxDevices)
+        return;
+    PdlNotes &n      = g_pdl_notes[device];
+    n.lo[n.next & 7] = (uintptr_t)p;
+    n.hi[n.next & 7] = (uintptr_t)p + bytes;
+    n.next++;
+}
+
+bool pdl_early_read_ok(int device, const void *p, size_t bytes)
+{
+    if (!p || !bytes)
+        return true;
+    if (device < 0 || device >= kMaxDevices)
+        return false;
+    const PdlNotes &n  = g_pdl_notes[device];
+    const uintptr_t lo = (uintptr_t)p, hi = lo + bytes;
+    for (int i = 0; i < 8; i++)
+        if (lo < n.hi[i] && n.lo[i] < hi)
+            return false;
+    return true;
+}
+
 void release(Scratch &s)
 {
     if (s.ptr)

@@ -294,10 +294,14 @@ static int launch_hist_t(DeviceCtx *c, unsigned *out256, unsigned *out64, const 
     at[1].id               = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs              = at;
-    cfg.numAttrs           = g_hist_pdl ? 2 : 1;
+    // the kernel streams `data` before its griddepcontrol.wait: only with the attribute when no early-releasing kernel
+    // in front can still be writing that range (internal.h: programmatic-launch guard)
+    cfg.numAttrs           = (g_hist_pdl && pdl_early_read_ok(c->device, d_data, n)) ? 2 : 1;
     B200_TRY(cudaLaunchKernelEx(&cfg, histogram_kernel<MODE, THREADS>, (const unsigned char *)d_data, n, out256, out64,
                                 (unsigned *)c->hist.ptr, p2p ? *p2p : P2PArgs()));
     count_launch();
+    pdl_note_output(c->device, out256, 256 * sizeof(unsigned));
+    pdl_note_output(c->device, out64, 64 * sizeof(unsigned));
     return 0;
 }
 

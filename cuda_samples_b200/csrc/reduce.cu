@@ -300,6 +300,15 @@ static int launch_reduce(const typename L::Elem *d_in, size_t n, typename L::Ele
                                                                     (Part *)chain_out, ReduceExchange(), reverse);
     count_launch();
     B200_TRY(cudaGetLastError());
+    // what this kernel writes while a dependent it has already released may be running (internal.h)
+    pdl_note_output(c->device, d_out, kernel_out_len * sizeof(Elem));
+    pdl_note_output(c->device, d_out_f64, sizeof(double));
+    pdl_note_output(c->device, chain_out, sizeof(Part));
+    if (ex) {
+        pdl_note_output(c->device, ex->gathered, sizeof(double) * ex->count * ex->p2p.world);
+        pdl_note_output(c->device, ex->sums, sizeof(double) * ex->count);
+        pdl_note_output(c->device, ex->carry, sizeof(unsigned));
+    }
     if (alias_out) {
         B200_TRY(cudaMemcpyAsync(alias_out, d_out, sizeof(Elem), cudaMemcpyDeviceToDevice, stream));
         if (out_len > 1)
@@ -580,6 +589,8 @@ extern "C" int b200_scan_exclusive_shard_async(uint32_t *d_dst, const uint32_t *
     scan_tile_sums_kernel<<<ntiles, kTileSumThreads, 0, stream>>>(d_src, n, tsum, ntiles, ticket, ex, true);
     B200_TRY(cudaGetLastError());
     count_launch();
+    pdl_note_output(c->device, d_work, sizeof(double) * (2 + a->world));
+    pdl_note_output(c->device, d_carry, sizeof(uint32_t));
     return scan_tiled(d_dst, d_src, n, tsum, stream);
 }
 

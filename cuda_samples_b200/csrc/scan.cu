@@ -866,7 +866,13 @@ static int launch_tma(K kernel, unsigned grid, size_t smem, cudaStream_t stream,
     cfg.attrs                                        = at;
     // measured (profiles/r02n_scan_shard_l2_pdl.log): the overlap pays for shards up to ~128 MiB (80.1 -> 76.5 us);
     // behind a longer total pass the early tiles only compete with it for HBM (2^27 elements: 286 -> 304 us)
-    cfg.numAttrs = (pdl && g_scan_pdl && (size_t)p.num_tiles * 8192u <= (40u << 20)) ? 1 : 0;
+    int dev = -1;
+    B200_TRY(cudaGetDevice(&dev));
+    // (tiles are bulk-loaded from d_src before griddepcontrol.wait: see the programmatic-launch guard in internal.h)
+    cfg.numAttrs = (pdl && g_scan_pdl && (size_t)p.num_tiles * 8192u <= (40u << 20) &&
+                    pdl_early_read_ok(dev, d_src, p.total * sizeof(uint32_t)))
+                       ? 1
+                       : 0;
     B200_TRY(cudaLaunchKernelEx(&cfg, kernel, d_dst, d_src, p, st64, desc));
     return 0;
 }
@@ -1061,7 +1067,9 @@ int scan_tiled(uint32_t *d_dst, const uint32_t *d_src, size_t n, const uint32_t 
     at[0].id                                         = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs                                        = at;
-    cfg.numAttrs                                     = g_scan_pdl ? 1 : 0;
+    int dev = -1;
+    B200_TRY(cudaGetDevice(&dev));
+    cfg.numAttrs = (g_scan_pdl && pdl_early_read_ok(dev, d_src, n * sizeof(uint32_t))) ? 1 : 0;
     unsigned           *no_state = nullptr;
     unsigned long long *no_desc  = nullptr;
     B200_TRY(cudaLaunchKernelEx(&cfg, scan_kernel<true>, d_dst, d_src, p, no_state, no_desc));

@@ -17,6 +17,12 @@
  * work on `stream`; they never synchronise.  The library keeps grow-only per-device scratch, so
  * calls on one device must be stream-ordered with each other (same contract as the samples'
  * file-static scratch: histogram256.cu:133, scan.cu:182, mergeSort.cu:452).
+ * Overlap between consecutive calls: the histogram kernels, and a scan given a d_carry, are launched with programmatic
+ * stream serialization and start reading their INPUT while the library kernel in front of them on the stream is still
+ * draining.  The library checks the input range against the outputs of its own recent launches on the device and
+ * launches the ordinary, fully ordered way when they overlap, so chains such as reduce -> histogram of its output
+ * buffer or histogram -> scan of the bins are safe; kernels that are not the library's never release early, so they
+ * are always waited for in full.
  */
 #ifndef B200PRIM_H
 #define B200PRIM_H

@@ -653,6 +653,38 @@ def test_scalar_prod(prim, vn, en):
 
 
 # ================================================================== CUDA graph capture / replay
+def test_a_kernel_that_overlaps_its_predecessor_never_reads_what_the_predecessor_is_still_writing(prim):
+    """reduce, histogram and the tile-sums pass release the next kernel on the stream at their very top, and the
+    histogram / the scan with a carry read their input before they wait for the kernel in front.  When that input IS
+    what the kernel in front writes (a histogram of the buffer a reduce zero-fills, a scan of fresh histogram bins),
+    the launcher must fall back to an ordinary, fully ordered launch (internal.h: programmatic-launch guard)."""
+    n_out = 8 << 20  # reduce leaves [sum, 0, 0, ...] in 32 MiB: the zero-fill takes the last CTA tens of microseconds
+    x = torch.ones(1 << 20, dtype=torch.int32, device="cuda")
+    for _ in range(5):
+        buf = torch.full((n_out,), -1, dtype=torch.int32, device="cuda")  # bytes 0xff everywhere
+        h = torch.empty(256, dtype=torch.int32, device="cuda")
+        prim.reduce(x.numel(), 256, n_out, 6, x, buf)
+        prim.histogram256(h, buf, 4 * n_out)  # histogram of the reduce's output buffer, same stream
+        got = h.cpu().numpy().view(np.uint32)
+        want = np.zeros(256, np.uint32)
+        for b in np.array([1 << 20], np.uint32).view(np.uint8):  # bytes of the sum
+            want[b] += 1
+        want[0] += 4 * n_out - 4
+        assert (got == want).all(), (int(got[0]), int(got[255]))
+    # scan (with a carry, the variant that is launched programmatically) of bins a histogram has just written
+    data = torch.from_numpy(np.random.default_rng(3).integers(0, 256, 1 << 26, dtype=np.uint8)).cuda()
+    carry = torch.tensor([5], dtype=torch.int32, device="cuda")
+    reps = 1 << 14  # 256 bins repeated: one array of 2^22 elements, long enough for the TMA-staged chained scan
+    for _ in range(5):
+        bins = torch.full((256 * reps,), 77, dtype=torch.int32, device="cuda")
+        out = torch.empty_like(bins)
+        prim.histogram256(bins[-256:], data, data.numel())  # overwrites the LAST 256 words: the scan's tail depends on them
+        prim.scanExclusiveLarge(out, bins, 1, bins.numel(), d_carry=carry)
+        hb = bins.cpu().numpy().view(np.uint32)
+        want = (np.concatenate(([0], np.cumsum(hb[:-1], dtype=np.uint32))) + np.uint32(5)).astype(np.uint32)
+        assert (out.cpu().numpy().view(np.uint32) == want).all()
+
+
 def test_entry_points_capture_into_a_cuda_graph_and_replay(prim):
     """Every *_async entry point only enqueues work on the given stream, and the kernels re-arm their own
     tickets / epochs on the device, so a captured sequence can be replayed (the inputs change between replays)."""
