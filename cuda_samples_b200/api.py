@@ -415,7 +415,7 @@ def host_probe_h2d_sustained(d_dst, h_src, nbytes, reps=4):
 
 
 def tune_host_path(mode, chunk_bytes=0):
-    """Experiments only: mode 0 = staged through device chunks, 1 = zero-copy for pinned input (default)."""
+    """Experiments only: mode 0 = staged through device chunks (default), 1 = zero-copy reads of pinned input."""
     check(lib.b200_tune_host_path(mode, chunk_bytes), "b200_tune_host_path")
 
 

@@ -70,12 +70,8 @@ __global__ void __launch_bounds__(32, 1) p2p_barrier_kernel(P2PArgs a)
 
 // One process, several devices: every device gets a window; with peer access enabled a peer's window is reachable
 // through its ordinary device pointer (unified addressing), so "connecting" is just filling in the tables.
-int p2p_connect_local(int ndev, const int *devices)
+static int p2p_connect_local_try(int ndev, const int *devices, bool *fresh)
 {
-    if (ndev < 1 || ndev > kP2PMaxRanks)
-        return (int)cudaErrorInvalidValue;
-    int prev = 0;
-    B200_TRY(cudaGetDevice(&prev));
     for (int i = 0; i < ndev; i++) {
         if (devices[i] < 0 || devices[i] >= kMaxDevices)
             return (int)cudaErrorInvalidDevice;
@@ -97,9 +93,30 @@ int p2p_connect_local(int ndev, const int *devices)
         }
         if (!s.own) {
             B200_TRY(cudaMalloc(&s.own, kP2PWindowBytes));
+            fresh[i] = true;
             B200_TRY(cudaMemset(s.own, 0, kP2PWindowBytes));
             B200_TRY(cudaDeviceSynchronize());
         }
+    }
+    return 0;
+}
+
+int p2p_connect_local(int ndev, const int *devices)
+{
+    if (ndev < 1 || ndev > kP2PMaxRanks)
+        return (int)cudaErrorInvalidValue;
+    int prev = 0;
+    B200_TRY(cudaGetDevice(&prev));
+    bool      fresh[kP2PMaxRanks] = {};
+    const int st                  = p2p_connect_local_try(ndev, devices, fresh);
+    if (st != 0) { // give back the windows this call created on the devices it got through before it failed
+        for (int i = 0; i < ndev; i++)
+            if (fresh[i] && cudaSetDevice(devices[i]) == cudaSuccess) {
+                cudaFree(g_p2p[devices[i]].own);
+                g_p2p[devices[i]].own = nullptr;
+            }
+        cudaSetDevice(prev);
+        return st;
     }
     for (int i = 0; i < ndev; i++) {
         P2PState &s = g_p2p[devices[i]];
@@ -184,16 +201,26 @@ int p2p_preload()
 
 using namespace b200;
 
-// How long a kernel waits for a peer's word before it gives up and counts an error (default 30 s).  Applies to the
-// current device's connected set; call after b200_p2p_connect / b200_ctx_create.
+// How long a kernel waits for a peer's word before it gives up and counts an error (default 30 s).
+// Current device connected (b200_p2p_connect / b200_ctx_create): applies to its connected set -- in the one-process
+// mode that is EVERY device of the context, not only the current one -- and to nothing else.  Current device not
+// connected: sets the value that sets connected later start with.
 extern "C" int b200_p2p_set_timeout_ms(unsigned ms)
 {
-    g_timeout_ns = (unsigned long long)(ms ? ms : 1) * 1000000ull;
-    int       st = 0;
-    P2PState *s  = p2p_state(&st);
+    const unsigned long long ns = (unsigned long long)(ms ? ms : 1) * 1000000ull;
+    int                      st = 0;
+    P2PState                *s  = p2p_state(&st);
     if (!s)
         return st;
-    s->args.timeout_ns = g_timeout_ns;
+    if (s->args.world == 0) {
+        g_timeout_ns = ns;
+        return 0;
+    }
+    s->args.timeout_ns = ns;
+    if (s->local) // the other devices of the same one-process set share this device's window table
+        for (int d = 0; d < kMaxDevices; d++)
+            if (g_p2p[d].local && g_p2p[d].args.world == s->args.world && g_p2p[d].args.win[0] == s->args.win[0])
+                g_p2p[d].args.timeout_ns = ns;
     return 0;
 }
 

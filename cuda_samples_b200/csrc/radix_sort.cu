@@ -327,8 +327,11 @@ __global__ void __launch_bounds__(kSortThreads)
                 peer.info[0] = col;
         }
         __syncthreads();
-        if (threadIdx.x == 0)
+        if (threadIdx.x == 0) {
             peer.info[1] = s_over;
+            if (s_over) // nothing will be sent: the local sort behind this exchange must find nothing to sort either
+                peer.info[0] = 0; // (the sizes that would be needed are in the matrix)
+        }
     }
 }
 

@@ -204,7 +204,9 @@ int b200_sort_kv_dyn_async(uint32_t *d_dstKey, uint32_t *d_dstVal, uint32_t *d_b
  * recvVals == NULL: recvKeys[r] are PAIR buffers (8 * capacity bytes): one 8-byte peer store per pair; sort them with
  * b200_sort_kv_dyn_async(..., d_srcKey = the own pair buffer, d_srcVal = NULL, ...).
  * d_matrix [world][world]
- * (row = source rank), d_info[0] = pairs received, d_info[1] != 0: a buffer would overflow, nothing was sent. */
+ * (row = source rank), d_info[0] = pairs received, d_info[1] != 0: a buffer would overflow, nothing was sent and
+ * d_info[0] = 0 (a b200_sort_kv_dyn_async behind this call then sorts nothing); the sizes needed are the column sums
+ * of d_matrix. */
 int b200_partition_exchange_kv_async(const uint32_t *d_srcKey, const uint32_t *d_srcVal, size_t N,
                                      const uint32_t *d_splitters, uint32_t sortDir, void *const *recvKeys,
                                      void *const *recvVals, size_t capacity, uint32_t *d_matrix, uint32_t *d_info,
@@ -218,7 +220,9 @@ int b200_histogram_fused_allreduce_async(uint32_t *d_hist256, uint32_t *d_hist64
  * memory, 3: cudaMemcpyAsync (copy engine; p2pBandwidthLatencyTest.cu:113-146).  Best of reps. */
 int b200_p2p_probe_store(void *d_dst, const void *d_src, size_t bytes, int mode, int reps, double *best_gbs,
                          b200_stream_t stream);
-/* how long a fused kernel waits for a peer's word before it gives up and counts an error (default 30 s) */
+/* how long a fused kernel waits for a peer's word before it gives up and counts an error (default 30 s).  With the
+ * current device connected it applies to that device's whole connected set (every device of a b200_ctx); otherwise it
+ * sets the value later connections start with. */
 int b200_p2p_set_timeout_ms(unsigned ms);
 /* splitters of the sharded sort chosen on the device (one exchange, no collective call, no host round trip):
  * d_splitters receives world-1 ascending values in ordered key space, identical on every rank */
@@ -243,8 +247,9 @@ int b200_ctx_synchronize(b200_ctx *ctx);
  * d_hist64[i] (64 u32) receive the GLOBAL bins.  Asynchronous: b200_ctx_synchronize before reading. */
 int b200_histogram_sharded(b200_ctx *ctx, uint32_t *const *d_hist256, uint32_t *const *d_hist64,
                            const void *const *d_data, const size_t *byteCount);
-/* sum over all shards, blocking.  int wraps like reduceCPU<int>; float/double: shard sums added in device order in
- * fp64 (deterministic), rounded once. */
+/* sum over all shards, blocking.  int wraps like reduceCPU<int>; float/double: every shard's sum is rounded to the
+ * element type (it is that device's reduce<T> result), the shard sums are added in device order in fp64
+ * (deterministic) and the total is rounded to the element type. */
 int b200_reduce_sharded_i32(b200_ctx *ctx, const int32_t *const *d_in, const size_t *n, int32_t *h_result);
 int b200_reduce_sharded_f32(b200_ctx *ctx, const float *const *d_in, const size_t *n, float *h_result);
 int b200_reduce_sharded_f64(b200_ctx *ctx, const double *const *d_in, const size_t *n, double *h_result);
@@ -253,7 +258,9 @@ int b200_scan_exclusive_sharded(b200_ctx *ctx, uint32_t *const *d_dst, const uin
 /* stable key-value sort of the concatenation of all shards; device i ends up with the i-th key range (h_nOut[i]
  * pairs) in d_dstKey[i] / d_dstVal[i] (dstCapacity pairs each; 1.25 x the largest shard is ample for random keys).
  * Blocking.  cudaErrorMemoryAllocation (2) when a device would receive more than dstCapacity pairs: nothing was
- * moved and h_nOut holds the sizes that are needed. */
+ * moved, the dst arrays are untouched and h_nOut holds the sizes that are needed.  The splitters are key values and
+ * do not break ties: all copies of one key go to one device, so a key that occurs more often than dstCapacity can
+ * only be sorted with a dstCapacity of at least that count. */
 int b200_sort_kv_sharded(b200_ctx *ctx, uint32_t *const *d_dstKey, uint32_t *const *d_dstVal, size_t dstCapacity,
                          const uint32_t *const *d_srcKey, const uint32_t *const *d_srcVal, const size_t *n,
                          uint32_t sortDir, size_t *h_nOut);

@@ -423,6 +423,28 @@ def test_sort_kat_sample_input(prim, kat):
         assert oracle.ref.validate_sorted_values(gk, gv, keys) == 1
 
 
+def test_sort_full_size_matches_mergeSortHost_hashes(prim):
+    """BASELINE.json configs[4] at its full 2^28 pairs against the reference's own mergeSortHost
+    (mergeSort_host.cpp:288-363), run once in the build container on the same counter-generated input (all keys
+    distinct, where mergeSortHost is the stable order; 321 s on one core) and committed as FNV-1a-64 hashes of its
+    output arrays: tests/golden/make_golden_sort_2p28.py -> tests/golden/kat_sort_2p28.json."""
+    import json
+    import os
+    with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "kat_sort_2p28.json")) as f:
+        m = json.load(f)
+    n = m["n"]
+    assert n == 1 << 28 and m["generated_by"] == "reference mergeSortHost"
+    sk = torch.empty(n, dtype=torch.int32, device="cuda")
+    prim.generate(sk, m["kind"], 0, n, m["seed"])
+    sv = torch.arange(n, dtype=torch.int64, device="cuda").to(torch.int32)
+    dk, dv, bk, bv = (torch.empty(n, dtype=torch.int32, device="cuda") for _ in range(4))
+    prim.mergeSort(dk, dv, bk, bv, sk, sv, n, m["dir"])
+    gk, gv = dk.cpu().numpy().view(np.uint32), dv.cpu().numpy().view(np.uint32)
+    assert [int(gk[0]), int(gv[0])] == m["first"] and [int(gk[-1]), int(gv[-1])] == m["last"]
+    assert hx(gk) == m["fnv_keys"]
+    assert hx(gv) == m["fnv_vals"]
+
+
 @pytest.mark.parametrize("dataset", ["d1", "d2"])
 def test_sort_matches_mergeSortHost_where_it_is_stable(prim, dataset):
     n = 1 << 20

@@ -96,8 +96,14 @@ def run_all(prim, devs, seed):
                 gv = np.concatenate([t[:m].cpu().numpy().view(np.uint32) for t, m in zip(dv, n_out)])
                 assert (gk == wk).all() and (gv == wv).all(), (kind, direction)
         if G > 1:
+            for t in dk + dv:
+                t.fill_(0x5A5A5A5A)
+            sync_all(devs)
             with pytest.raises(prim.B200Error):
                 ctx.sort_kv(dk, dv, n // 4, sk, sv, [n] * G, 1)
+            sync_all(devs)
+            for t in dk + dv:  # "nothing was moved": the destination arrays are as the caller left them
+                assert bool((t == 0x5A5A5A5A).all())
             n_out = ctx.sort_kv(dk, dv, cap, sk, sv, [n] * G, 1)  # and the context is still usable afterwards
             assert sum(n_out) == G * n
     finally:

@@ -4,6 +4,8 @@ The restatement in oracle/oracle.c must agree with
   * the committed golden vectors (tests/golden/, produced by the reference's own gold code), and
   * the reference gold compiled unmodified (oracle/_ref/libref_gold.so) whenever that file exists.
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -231,3 +233,16 @@ def test_integral_image_oracle_matches_the_samples_checks():
         want = np.cumsum(np.cumsum(img.astype(np.uint64), axis=1), axis=0).astype(np.uint32)
         assert (oracle.integral_image(img) == want).all()
     assert oracle.integral_image(np.zeros((0, 4), np.uint8)).size == 0
+
+
+def test_full_size_mergeSortHost_fixture_is_what_its_script_writes():
+    """tests/golden/kat_sort_2p28.json: hashes of the reference's mergeSortHost at 2^28 pairs (5 minutes of CPU, so it
+    is not re-run here); its first and last pairs can be checked against the generator in a moment: with distinct
+    keys the first output pair is the smallest key with its index."""
+    import json
+    with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "kat_sort_2p28.json")) as f:
+        m = json.load(f)
+    assert m["n"] == 1 << 28 and m["kind"] == "key_unique" and m["dir"] == 1
+    assert len(m["fnv_keys"]) == 16 and len(m["fnv_vals"]) == 16
+    for key, idx in (m["first"], m["last"]):
+        assert int(oracle.generate("key_unique", idx, 1, m["seed"], 0)[0]) == key
