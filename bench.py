@@ -530,7 +530,123 @@ def primitives_table(torch, dist, prim, mg, rank, world, peak, barrier, p2p=Fals
                 "note": "SM-bound, not HBM-bound: two stable radix passes (16-bit keys) + one on the array index, "
                         "~70 instructions per pair per pass; the sample's 2^20-pair shapes are one wave of CTAs"}
             del bsk, bsv, bdk, bdv
+        torch.cuda.empty_cache()
+        isolated_and_host_rows(torch, prim, table, peak)
     return table
+
+
+def isolated_and_host_rows(torch, prim, table, peak):
+    """(1) The 64 MiB histogram as ONE call between synchronisations (the rows above time 40 calls back to back, where
+    call k+1 overlaps the drain of call k through programmatic dependent launch: a caller who histograms once gets
+    this row instead).  (2) histogram / scan / sort through the host-buffer ABI (b200_*_host: pinned host memory in,
+    host memory out, copies inside the call, wall clock) -- the callers' view of histogram/main.cpp:136-170,
+    scan/main.cpp:59-61,87 and mergeSort/main.cpp:80-97 with their cudaMemcpy's counted."""
+    import numpy as np
+    n64 = 64 << 20
+    bufs = [torch.empty(n64, dtype=torch.uint8, device="cuda") for _ in range(4)]
+    for i, b in enumerate(bufs):
+        prim.generate(b, "bytes", i * n64, n64, 2009)
+    h256 = torch.empty(256, dtype=torch.int32, device="cuda")
+    times = []
+    for i in range(24):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        prim.histogram256(h256, bufs[i & 3], n64)
+        e1.record()
+        torch.cuda.synchronize()
+        if i >= 4:
+            times.append(e0.elapsed_time(e1) * 1e-3)
+    t = float(np.median(times))
+    table["histogram256_64MiB"]["mode"] = "back to back: 40 calls on one stream, consecutive calls overlap (PDL)"
+    table["histogram64_64MiB"]["mode"] = table["histogram256_64MiB"]["mode"]
+    table["histogram256_64MiB_isolated"] = {
+        "GB/s": round(n64 / t / 1e9, 1), "us_per_call": round(t * 1e6, 2), "algorithmic_bytes": n64,
+        "frac_of_measured_peak": round(n64 / t / 1e9 / peak, 4), "n_gpus": 1,
+        "mode": "isolated: one call between device synchronisations, CUDA events around it (launch latency "
+                "included), median of 20"}
+    del bufs
+
+    def wall(fn, reps=3):
+        fn()
+        best = None
+        for _ in range(reps):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            fn()
+            dt = time.perf_counter() - t0
+            best = dt if best is None or dt < best else best
+        return best
+
+    def pinned(nbytes, dtype):
+        hb = prim.HostBuffer(nbytes)
+        return hb, hb.array(dtype)
+
+    def fill(host_arr, dev_tensor):
+        torch.from_numpy(host_arr.view(np.uint8)).copy_(dev_tensor.view(torch.uint8))
+
+    def host_row(name, t, h2d, d2h, pcie, units, unit_name, api, ok, gold_row):
+        row = {"seconds": round(t, 5), "h2d_bytes": h2d, "d2h_bytes": d2h, "api": api,
+               unit_name: round(units / t / 1e9, 3), "GB/s_h2d": round(h2d / t / 1e9, 2),
+               "pcie_gbs_h2d_probe": round(pcie, 2),
+               "frac_of_pcie": round(max(h2d, d2h) / t / 1e9 / pcie, 4) if pcie else None,
+               "frac_of_pcie_note": "the larger direction's bytes / time over the same-run pinned H2D probe (the two "
+                                    "directions can overlap: PCIe is full duplex)",
+               "result_equals_device_path": bool(ok), "cpu_gold_row": gold_row, "n_gpus": 1}
+        table[name] = row
+
+    # histogram: 64 MiB and 4 GiB of pinned bytes -> 256 bins
+    for label, nb in (("64MiB", 64 << 20), ("4GiB", 4 << 30)):
+        d = torch.empty(nb, dtype=torch.uint8, device="cuda")
+        prim.generate(d, "bytes", 0, nb, 2009)
+        hb, ha = pinned(nb, np.uint8)
+        fill(ha, d)
+        want = torch.empty(256, dtype=torch.int32, device="cuda")
+        prim.histogram256(want, d, nb)
+        del d
+        pcie = prim.host_probe_h2d(ha, nb, 3)
+        got = [None]
+
+        def step_h():
+            got[0] = prim.histogram256_host(ha)
+        t = wall(step_h)
+        host_row("e2e_histogram256_" + label, t, nb, 1024, pcie, nb, "GB/s", "b200_histogram256_host",
+                 (got[0] == want.cpu().numpy().view(np.uint32)).all(), "histogram256")
+        hb.free()
+    # scan: 2^28 u32 in, 2^28 u32 out
+    n = N_ELEMS
+    src = torch.empty(n, dtype=torch.int32, device="cuda")
+    prim.generate(src, "u31", 0, n, 2009)
+    hb_s, hs = pinned(4 * n, np.uint32)
+    hb_d, hd = pinned(4 * n, np.uint32)
+    fill(hs, src)
+    want = torch.empty_like(src)
+    prim.scanExclusiveLarge(want, src, 1, n)
+    pcie = prim.host_probe_h2d(hs, 4 * n, 3)
+    t = wall(lambda: prim.scan_exclusive_host(hd, hs, 1, n))
+    src.copy_(torch.from_numpy(hd.view(np.int32)))
+    host_row("e2e_scanExclusiveLarge_2^28", t, 4 * n, 4 * n, pcie, 8 * n, "GB/s_in+out", "b200_scan_exclusive_host",
+             torch.equal(src, want), "scanExclusiveHost")
+    del src, want
+    hb_s.free(), hb_d.free()
+    # key-value sort: 2^28 pairs in, 2^28 pairs out
+    sk = torch.empty(n, dtype=torch.int32, device="cuda")
+    prim.generate(sk, "key_unique", 0, n, 2009)
+    sv = torch.arange(n, dtype=torch.int64, device="cuda").to(torch.int32)
+    hbs = [pinned(4 * n, np.uint32) for _ in range(4)]
+    (hsk, hsv, hdk, hdv) = [a for _, a in hbs]
+    fill(hsk, sk), fill(hsv, sv)
+    dk, dv, bk, bv = (torch.empty(n, dtype=torch.int32, device="cuda") for _ in range(4))
+    prim.mergeSort(dk, dv, bk, bv, sk, sv, n, 1)
+    del bk, bv, sk, sv
+    pcie = prim.host_probe_h2d(hsk, 4 * n, 3)
+    t = wall(lambda: prim.sort_kv_host(hdk, hdv, hsk, hsv, n, 1), reps=2)
+    ok = bool((torch.from_numpy(hdk.view(np.int32)) == dk.cpu()).all()) and \
+        bool((torch.from_numpy(hdv.view(np.int32)) == dv.cpu()).all())
+    host_row("e2e_mergeSort_kv_2^28", t, 8 * n, 8 * n, pcie, n, "Gkeys/s", "b200_sort_kv_host", ok, "mergeSortHost")
+    del dk, dv
+    for hb, _ in hbs:
+        hb.free()
 
 
 # ------------------------------------------------------------------------------------------- parity
@@ -852,12 +968,20 @@ def run_ours(args):
         except Exception as e:
             cpu_gold = {"error": repr(e)}
 
-    traffic = None
+    # dram bytes per launch of reduce_kernel from the committed `ncu --set full` capture -- only if that capture was of
+    # the kernel that runs now (profiles/summarize.py stores a hash of the kernel's sources beside the figure)
+    traffic, traffic_source = None, None
     try:
+        sys.path.insert(0, os.path.join(ROOT, "profiles"))
+        from summarize import reduce_source_hash
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            traffic = json.load(f).get("reduce_kernel")
-    except Exception:
-        pass
+            tj = json.load(f)
+        if tj.get("_reduce_source_sha256") == reduce_source_hash():
+            traffic, traffic_source = tj.get("reduce_kernel"), tj.get("_source")
+        else:
+            traffic_source = "profiles/traffic.json was captured from other sources of reduce_kernel: figure withheld"
+    except Exception as e:
+        traffic_source = "unavailable: %r" % (e,)
     cfg = base_config(world)  # identical to the reference arm's config: the same workload, nothing else in here
     notes = {"clock_probe": "same step looped ~1.5 s after the timed region for the 100 ms nvidia-smi poller"}
     if world > 1:
@@ -869,7 +993,7 @@ def run_ours(args):
             "scaling": "weak", "vs_baseline": None, "dtype": "i32+f32", "data": "synthetic", "config": cfg,
             "roofline": {"bound": "hbm", "kernel": "reduce_kernel<int|float>", "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
-                         "frac_of_nominal_8TBs": achieved / HBM_NOMINAL, "traffic": traffic,
+                         "frac_of_nominal_8TBs": achieved / HBM_NOMINAL, "traffic": traffic, "traffic_source": traffic_source,
                          "algorithmic_bytes_per_launch": 4 * N_ELEMS},
             "cpu_baseline": cpu, "cpu_gold": cpu_gold, "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": 2 * 4 * N_ELEMS * world,

@@ -17,6 +17,17 @@ WANT = ["Kernel Name", "launch__grid_size", "launch__block_size", "launch__regis
 SCALE = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}
 
 
+def reduce_source_hash():
+    """sha256 over the sources reduce_kernel is compiled from: ties profiles/traffic.json to the kernel that is timed."""
+    import hashlib
+    csrc = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "cuda_samples_b200", "csrc")
+    h = hashlib.sha256()
+    for name in ("reduce.cu", "common.cuh", "p2p.cuh", "internal.h"):
+        with open(os.path.join(csrc, name), "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()
+
+
 def main(rep, out):
     raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(raw.splitlines()))
@@ -38,6 +49,7 @@ def main(rep, out):
     red = [v for k, v in summary.items() if "reduce_kernel" in k]
     if red:
         summary["reduce_kernel"] = max(red)
+    summary["_reduce_source_sha256"] = reduce_source_hash()  # bench.py refuses the figure when the kernel has changed
     summary["_source"] = os.path.basename(rep) + ": ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per launch"
     tj = os.path.join(os.path.dirname(os.path.abspath(out)), "traffic.json")
     try:  # a capture restricted with -k keeps the other kernels' earlier figures
