@@ -77,6 +77,29 @@ def run_all(prim, devs, seed):
             assert (t.cpu().numpy().view(np.uint32) == want[off:off + n]).all()
             off += n
 
+        # ---- the sharded scan 24 times back to back, no host synchronisation in between, short peer timeout: a device
+        #      that ran ahead of its peers' reads of the exchange windows would lose a word, and synchronize() raises
+        if G > 1:
+            ns2 = [(1 << 20) + 8192 * i for i in range(G)]  # every shard takes the tile-prefix path
+            src2 = [rng.integers(0, 2**32, n, dtype=np.uint32) for n in ns2]
+            d_src2 = [on(d, s.view(np.int32)) for d, s in zip(devs, src2)]
+            d_dst2 = [torch.empty_like(t) for t in d_src2]
+            sync_all(devs)
+            torch.cuda.set_device(devs[0])
+            prim.p2p_set_timeout_ms(2000)  # (applies to every device of the context)
+            try:
+                for _ in range(24):
+                    ctx.scan_exclusive(d_dst2, d_src2, ns2)
+                ctx.synchronize()
+            finally:
+                prim.p2p_set_timeout_ms(30000)
+            whole = np.concatenate(src2)
+            want = oracle.scan_exclusive(whole, 1, whole.size)
+            off = 0
+            for t, n in zip(d_dst2, ns2):
+                assert (t.cpu().numpy().view(np.uint32) == want[off:off + n]).all()
+                off += n
+
         # ---- sort: three key distributions, both directions; too small a capacity is a status, not a crash
         n = 1 << 20
         cap = int(1.5 * n) if G > 1 else n
